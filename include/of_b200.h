@@ -1,0 +1,168 @@
+/* of_b200.h -- C ABI of the B200-native dense pyramidal Lucas-Kanade path.
+ *
+ * This is the drop-in boundary.  The reference
+ * (mileslindheimer/optical-flow) has no plugin/FFI interface: its boundary is the set
+ * of C++ free functions every main() calls.  Each entry point below names the
+ * reference function it replaces (file:line into the reference repository; line
+ * numbers are ParallelVideoPyr.cpp's, serial twin ctfLKof.cpp:121-215).  A header-only
+ * C++ shim with the reference's own function names lives in of_b200_shim.hpp.
+ *
+ * Layout conventions (== the reference's cv::Mat CV_64FC1 convention):
+ *   frames and flow planes are single-channel, row-major double; element (y,x) is at
+ *   (char*)base + y*step_bytes + x*8.  step_bytes may exceed width*8 (ROI views) and
+ *   must be a multiple of 8.  u = x-flow, v = y-flow, two separate planes.
+ *   mask (optional, may be NULL): uint8 plane, 1 where the level-0 2x2 system passed
+ *   the validity rule (|det| > det_eps; det != 0 with the reference's det_eps = 0).
+ *
+ * All functions are extern "C", POD-only, and never throw.  A context is bound to one
+ * CUDA device and is not thread-safe; distinct contexts may be used concurrently from
+ * distinct threads/processes (the multi-GPU model: one process or thread per GPU).
+ * There is NO CPU fallback: if no CUDA device is usable, of_ctx_create fails with
+ * OF_E_CUDA.
+ */
+#ifndef OF_B200_H_
+#define OF_B200_H_
+
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define OF_B200_ABI_VERSION 1
+
+#if defined(__GNUC__)
+#define OF_API __attribute__((visibility("default")))
+#else
+#define OF_API
+#endif
+
+typedef struct of_ctx of_ctx;
+typedef int of_status;
+
+enum {
+    OF_OK = 0,
+    OF_E_BADARG = 1,        /* null pointer, width/height < 1, n_levels < 1, bad step  */
+    OF_E_NOT_DIVISIBLE = 2, /* width or height % 2^(n_levels-1) != 0: the reference      */
+                            /* throws a cv::Exception at tmpu += upu (:635), quirk Q2    */
+    OF_E_CUDA = 3,          /* CUDA runtime/driver error; see of_last_error_string       */
+    OF_E_NOMEM = 4          /* device or host allocation failed                          */
+};
+
+typedef struct of_params {
+    int win_radius;        /* window radius r, window = (2r+1)^2.  Reference: 1 (get_Sum9,   */
+                           /* :114-160).  BASELINE throughput config: 7 (15x15).  1..15.     */
+    double det_eps;        /* validity: |det| > det_eps.  Reference: 0.0 (cv::divide's        */
+                           /* zero-divisor -> 0 rule, :514,518).                              */
+    int write_back_warped; /* 1: host-pointer of_ctf_f64 overwrites img1/img2 with their      */
+                           /* warped level-0 versions like the reference does (quirk Q1,      */
+                           /* warped.copyTo(pyr[i-1]) :696,701).  Default 0: inputs const.    */
+    double mag_thresh;     /* gesture statistics: flow magnitude threshold, reference 20 (:859)*/
+    int count_thresh;      /* gesture present iff count > count_thresh, reference 500 (:886)  */
+} of_params;
+
+/* Per-pair gesture statistics (ParallelVideoPyr.cpp:845-888, headless replacement of
+ * circle()+imshow()): sums of x (column) and y (row) indices and the count of pixels
+ * whose flow magnitude is not < mag_thresh. */
+typedef struct of_gesture_stats {
+    double sum_x;
+    double sum_y;
+    double count;     /* integer-valued */
+    double detected;  /* 1.0 iff count > count_thresh */
+} of_gesture_stats;
+
+/* Fills *p with the reference's constants (r=1, det_eps=0, no write-back, 20, 500). */
+OF_API void of_params_default(of_params *p);
+
+/* Replaces: int getMaxLayer(Mat &img)   ParallelVideoPyr.cpp:545-564 (ctfLKof.cpp:196-215).
+ * min over width/height of 1 + (number of times 2 divides n).  Returns 0 for empty sizes. */
+OF_API int of_get_max_layer(int width, int height);
+
+/* Context: owns a CUDA stream and all device scratch (pyramids, per-level flows, staging
+ * buffers); scratch is sized on first use per (width, height, n_levels, batch) and reused.
+ * params may be NULL (reference defaults). */
+OF_API of_status of_ctx_create(int device, const of_params *params, of_ctx **out);
+OF_API void of_ctx_destroy(of_ctx *ctx);
+OF_API of_status of_ctx_set_params(of_ctx *ctx, const of_params *params);
+OF_API const char *of_last_error_string(const of_ctx *ctx); /* ctx may be NULL: last create error */
+OF_API int of_abi_version(void);
+
+/* ---- host-pointer entry points (synchronous; H2D + compute + D2H) ----------------------- */
+
+/* Replaces: void getLucasKanadeOpticalFlow(Mat &img1, Mat &img2, Mat &u, Mat &v)
+ *           ParallelVideoPyr.cpp:327-542 (ctfLKof.cpp:121-144).  Single level, no pyramid. */
+OF_API of_status of_lk_single_f64(of_ctx *ctx, const double *img1, const double *img2,
+                           int width, int height, size_t step_bytes,
+                           double *u, double *v, size_t uv_step_bytes,
+                           unsigned char *mask, size_t mask_step_bytes);
+
+/* Replaces: void coarseToFineEstimation(Mat &img1, Mat &img2, Mat &u, Mat &v, int nLevels)
+ *           ParallelVideoPyr.cpp:578-725 (ctfLKof.cpp:157-194), including
+ *           getGaussianPyramid :566-575.  img1/img2 are written only when
+ *           params.write_back_warped = 1 (hence non-const). */
+OF_API of_status of_ctf_f64(of_ctx *ctx, double *img1, double *img2,
+                     int width, int height, size_t step_bytes, int n_levels,
+                     double *u, double *v, size_t uv_step_bytes,
+                     unsigned char *mask, size_t mask_step_bytes);
+
+/* Frame stream, host pointers: n_frames frames, frame k at (char*)frames + k*frame_stride_bytes;
+ * computes the n_frames-1 consecutive pairs (k, k+1) (the live loop's pairing,
+ * ParallelVideoPyr.cpp:831-843, with inputs read-only) and writes flow k at
+ * (char*)u + k*uv_pair_stride_bytes.  u/v may be NULL when only stats are wanted; stats may
+ * be NULL.  Uploads are chunked and overlapped with compute on the context's streams. */
+OF_API of_status of_ctf_f64_stream(of_ctx *ctx, const double *frames, int n_frames,
+                            size_t frame_stride_bytes, int width, int height,
+                            size_t step_bytes, int n_levels,
+                            double *u, double *v, size_t uv_pair_stride_bytes,
+                            size_t uv_step_bytes, of_gesture_stats *stats);
+
+/* ---- device-pointer entry points (stream-ordered, asynchronous) -------------------------- */
+/* All pointers are device pointers on the context's device.  stream is a cudaStream_t passed
+ * as void* (NULL = the context's own stream).  These are what the benchmark's device-resident
+ * number times. */
+
+OF_API of_status of_lk_single_f64_dev(of_ctx *ctx, const double *img1, const double *img2,
+                               int width, int height, size_t step_bytes,
+                               double *u, double *v, size_t uv_step_bytes,
+                               unsigned char *mask, size_t mask_step_bytes, void *stream);
+
+OF_API of_status of_ctf_f64_dev(of_ctx *ctx, const double *img1, const double *img2,
+                         int width, int height, size_t step_bytes, int n_levels,
+                         double *u, double *v, size_t uv_step_bytes,
+                         unsigned char *mask, size_t mask_step_bytes, void *stream);
+
+/* Batch of independent pairs: pair k reads img1 + k*img_pair_stride_bytes and
+ * img2 + k*img_pair_stride_bytes, writes u/v + k*uv_pair_stride_bytes.  A video stream is the
+ * special case img2 = img1 + one frame, img_pair_stride = one frame.  stats (device pointer to
+ * n_pairs of_gesture_stats, may be NULL) receives the gesture statistics of every pair;
+ * u and v may both be NULL when only stats are wanted. */
+OF_API of_status of_ctf_f64_batch_dev(of_ctx *ctx, int n_pairs,
+                               const double *img1, const double *img2,
+                               size_t img_pair_stride_bytes,
+                               int width, int height, size_t step_bytes, int n_levels,
+                               double *u, double *v, size_t uv_pair_stride_bytes,
+                               size_t uv_step_bytes,
+                               unsigned char *mask, size_t mask_pair_stride_bytes,
+                               size_t mask_step_bytes,
+                               of_gesture_stats *stats, void *stream);
+
+/* Gesture statistics of existing flow planes (ParallelVideoPyr.cpp:845-873). */
+OF_API of_status of_gesture_stats_dev(of_ctx *ctx, int n_pairs, const double *u, const double *v,
+                               size_t uv_pair_stride_bytes, int width, int height,
+                               size_t uv_step_bytes, of_gesture_stats *stats, void *stream);
+
+/* Building blocks, exposed for parity triage (each is one reference/OpenCV call site). */
+/* cv::pyrDown at getGaussianPyramid :571.  dst is ((w+1)/2) x ((h+1)/2). */
+OF_API of_status of_pyr_down_f64_dev(of_ctx *ctx, const double *src, int width, int height,
+                              size_t step_bytes, double *dst, size_t dst_step_bytes, void *stream);
+
+/* Blocks until everything queued on the context's own stream has finished. */
+OF_API of_status of_ctx_synchronize(of_ctx *ctx);
+
+/* Number of kernel launches issued through this context since creation (bench evidence). */
+OF_API unsigned long long of_ctx_launch_count(const of_ctx *ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* OF_B200_H_ */

@@ -1,0 +1,644 @@
+// C-ABI layer (include/of_b200.h) over the sm_100a kernels: context, device scratch,
+// level scheduling of coarseToFineEstimation (ParallelVideoPyr.cpp:578-725) and the
+// host-pointer / device-pointer / batch / stream entry points.
+//
+// There is no CPU path in this file: every entry point either launches the CUDA kernels
+// or returns an error code.
+#include <cuda_runtime.h>
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "of_kernels.h"
+
+namespace ofb {
+cudaError_t launch_lk_level_tile(const LevelArgs& a, int n_pairs, cudaStream_t s,
+                                 unsigned long long* launches);
+cudaError_t launch_lk_level_march(const LevelArgs& a, int n_pairs, cudaStream_t s,
+                                  unsigned long long* launches, bool* handled);
+}  // namespace ofb
+
+namespace {
+
+std::string g_create_error;
+
+size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+struct Arena {
+    char* base = nullptr;
+    size_t cap = 0;
+};
+
+}  // namespace
+
+struct of_ctx {
+    int device = 0;
+    of_params params{};
+    cudaStream_t stream = nullptr;     // compute stream owned by the context
+    cudaStream_t copy_stream = nullptr;  // H2D uploads of the stream entry point
+    cudaStream_t down_stream = nullptr;  // D2H downloads of the stream entry point
+    cudaEvent_t ev_up[2] = {nullptr, nullptr};
+    cudaEvent_t ev_done[2] = {nullptr, nullptr};
+    cudaEvent_t ev_down[2] = {nullptr, nullptr};
+    Arena scratch;                     // pyramids + per-level flows
+    Arena staging;                     // device copies of host-pointer inputs/outputs
+    std::string err;
+    unsigned long long launches = 0;
+    int force_variant = 0;             // 0 auto, 1 tile, 2 march (test hook via OF_B200_VARIANT)
+};
+
+namespace {
+
+of_status fail(of_ctx* ctx, of_status code, const char* fmt, ...)
+{
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    if (ctx) ctx->err = buf; else g_create_error = buf;
+    return code;
+}
+
+#define OF_CUDA(ctx, call)                                                                  \
+    do {                                                                                    \
+        cudaError_t e_ = (call);                                                            \
+        if (e_ != cudaSuccess)                                                              \
+            return fail(ctx, e_ == cudaErrorMemoryAllocation ? OF_E_NOMEM : OF_E_CUDA,       \
+                        "%s failed: %s", #call, cudaGetErrorString(e_));                    \
+    } while (0)
+
+of_status arena_reserve(of_ctx* ctx, Arena& a, size_t bytes)
+{
+    if (bytes <= a.cap) return OF_OK;
+    if (a.base) {
+        OF_CUDA(ctx, cudaDeviceSynchronize());
+        OF_CUDA(ctx, cudaFree(a.base));
+        a.base = nullptr;
+        a.cap = 0;
+    }
+    bytes = align_up(bytes + bytes / 8, (size_t)1 << 20);
+    void* p = nullptr;
+    cudaError_t e = cudaMalloc(&p, bytes);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return fail(ctx, OF_E_NOMEM, "cudaMalloc(%zu bytes) failed: %s", bytes, cudaGetErrorString(e));
+    }
+    a.base = (char*)p;
+    a.cap = bytes;
+    return OF_OK;
+}
+
+struct LevelGeom {
+    int w, h;
+    size_t pitch;       // doubles
+    size_t img_stride;  // doubles
+};
+
+// Scratch layout for one batch.
+struct Plan {
+    int L = 0, n_pairs = 0, n_frames = 0;  // n_frames: images per pyramid level
+    bool shared = false;                   // stream mode: frame k+1 of pair k is frame k of pair k+1
+    std::vector<LevelGeom> g;              // per level
+    std::vector<size_t> pyr_off;           // byte offset of level l's images (l >= 1)
+    std::vector<size_t> flow_u_off, flow_v_off;
+    size_t total = 0;
+};
+
+Plan make_plan(int w, int h, int L, int n_pairs, bool shared)
+{
+    Plan p;
+    p.L = L;
+    p.n_pairs = n_pairs;
+    p.shared = shared;
+    p.n_frames = shared ? n_pairs + 1 : 2 * n_pairs;
+    p.g.resize(L);
+    p.pyr_off.assign(L, 0);
+    p.flow_u_off.assign(L, 0);
+    p.flow_v_off.assign(L, 0);
+    size_t off = 0;
+    for (int l = 0; l < L; ++l) {
+        LevelGeom& g = p.g[l];
+        g.w = w >> l;
+        g.h = h >> l;
+        g.pitch = align_up((size_t)g.w, 16);             // 128-byte rows
+        g.img_stride = align_up(g.pitch * (size_t)g.h, 32);
+        if (l >= 1) {
+            p.pyr_off[l] = off;
+            off += g.img_stride * p.n_frames * sizeof(double);
+            p.flow_u_off[l] = off;
+            off += g.img_stride * n_pairs * sizeof(double);
+            p.flow_v_off[l] = off;
+            off += g.img_stride * n_pairs * sizeof(double);
+        }
+    }
+    p.total = off;
+    return p;
+}
+
+of_status check_common(of_ctx* ctx, const void* a, const void* b, int w, int h, size_t step,
+                       int L)
+{
+    if (!ctx) return OF_E_BADARG;
+    if (!a || !b) return fail(ctx, OF_E_BADARG, "null frame pointer");
+    if (w < 1 || h < 1) return fail(ctx, OF_E_BADARG, "width/height must be >= 1 (got %dx%d)", w, h);
+    if (w > 32767 || h > 32767)
+        return fail(ctx, OF_E_BADARG, "width/height above 32767 are not representable in remap's int16 coordinates");
+    if (step % sizeof(double) || step < (size_t)w * sizeof(double))
+        return fail(ctx, OF_E_BADARG, "step_bytes %zu invalid for width %d", step, w);
+    if (L < 1 || L > 24) return fail(ctx, OF_E_BADARG, "n_levels must be in 1..24 (got %d)", L);
+    const int f = 1 << (L - 1);
+    if (w % f || h % f)
+        return fail(ctx, OF_E_NOT_DIVISIBLE, "%dx%d is not divisible by 2^(n_levels-1) = %d", w, h, f);
+    return OF_OK;
+}
+
+cudaError_t launch_lk_level(of_ctx* ctx, const ofb::LevelArgs& a, int n_pairs, cudaStream_t s)
+{
+    if (ctx->force_variant != 1) {
+        bool handled = false;
+        cudaError_t e = ofb::launch_lk_level_march(a, n_pairs, s, &ctx->launches, &handled);
+        if (handled || e != cudaSuccess) return e;
+        if (ctx->force_variant == 2) return cudaErrorNotSupported;
+    }
+    return ofb::launch_lk_level_tile(a, n_pairs, s, &ctx->launches);
+}
+
+// Core: all device pointers, stream-ordered.
+of_status run_batch(of_ctx* ctx, int n_pairs, const double* img1, const double* img2,
+                    size_t img_pair_stride, int w, int h, size_t step, int L, double* u,
+                    double* v, size_t uv_pair_stride, size_t uv_step, unsigned char* mask,
+                    size_t mask_pair_stride, size_t mask_step, of_gesture_stats* stats,
+                    cudaStream_t s)
+{
+    of_status st = check_common(ctx, img1, img2, w, h, step, L);
+    if (st) return st;
+    if (n_pairs < 1) return fail(ctx, OF_E_BADARG, "n_pairs must be >= 1");
+    if ((u == nullptr) != (v == nullptr)) return fail(ctx, OF_E_BADARG, "u and v must both be given or both be NULL");
+    if (!u && !stats && !mask) return fail(ctx, OF_E_BADARG, "nothing to compute: u, v, mask and stats are all NULL");
+    if (u && (uv_step % sizeof(double) || uv_step < (size_t)w * sizeof(double)))
+        return fail(ctx, OF_E_BADARG, "uv_step_bytes %zu invalid for width %d", uv_step, w);
+    if (mask && mask_step < (size_t)w) return fail(ctx, OF_E_BADARG, "mask_step_bytes %zu < width", mask_step);
+    if (n_pairs > 1 && img_pair_stride % sizeof(double))
+        return fail(ctx, OF_E_BADARG, "img_pair_stride_bytes must be a multiple of 8");
+    if (u && n_pairs > 1 && uv_pair_stride % sizeof(double))
+        return fail(ctx, OF_E_BADARG, "uv_pair_stride_bytes must be a multiple of 8");
+    if (ctx->params.win_radius < 1 || ctx->params.win_radius > 15)
+        return fail(ctx, OF_E_BADARG, "win_radius must be in 1..15");
+    OF_CUDA(ctx, cudaSetDevice(ctx->device));
+
+    const bool shared = n_pairs > 1 && (const char*)img2 == (const char*)img1 + img_pair_stride;
+    Plan p = make_plan(w, h, L, n_pairs, shared);
+    st = arena_reserve(ctx, ctx->scratch, p.total);
+    if (st) return st;
+    char* base = ctx->scratch.base;
+    const size_t in_pitch = step / sizeof(double);
+    const size_t in_stride = img_pair_stride / sizeof(double);
+
+    // ---- Gaussian pyramids (getGaussianPyramid :566-575, both frames :587-597) ------------
+    for (int l = 1; l < L; ++l) {
+        const LevelGeom& gs = p.g[l - 1];
+        const LevelGeom& gd = p.g[l];
+        double* dst = (double*)(base + p.pyr_off[l]);
+        ofb::PyrDownArgs a{};
+        a.w = gs.w;
+        a.h = gs.h;
+        a.dst_pitch = gd.pitch;
+        a.dst_img_stride = gd.img_stride;
+        if (l == 1) {
+            a.src_pitch = in_pitch;
+            a.src_img_stride = in_stride;
+            if (shared) {
+                a.src = img1; a.dst = dst; a.n_images = n_pairs + 1;
+                OF_CUDA(ctx, ofb::launch_pyr_down(a, s, &ctx->launches));
+            } else {
+                a.src = img1; a.dst = dst; a.n_images = n_pairs;
+                OF_CUDA(ctx, ofb::launch_pyr_down(a, s, &ctx->launches));
+                a.src = img2; a.dst = dst + gd.img_stride * n_pairs;
+                OF_CUDA(ctx, ofb::launch_pyr_down(a, s, &ctx->launches));
+            }
+        } else {
+            a.src = (const double*)(base + p.pyr_off[l - 1]);
+            a.src_pitch = gs.pitch;
+            a.src_img_stride = gs.img_stride;
+            a.dst = dst;
+            a.n_images = p.n_frames;
+            OF_CUDA(ctx, ofb::launch_pyr_down(a, s, &ctx->launches));
+        }
+    }
+
+    if (stats) OF_CUDA(ctx, cudaMemsetAsync(stats, 0, sizeof(of_gesture_stats) * n_pairs, s));
+
+    // ---- coarse to fine (:610-703), one fused launch per level ----------------------------
+    for (int l = L - 1; l >= 0; --l) {
+        const LevelGeom& g = p.g[l];
+        ofb::LevelArgs a{};
+        a.w = g.w;
+        a.h = g.h;
+        a.radius = ctx->params.win_radius;
+        a.det_eps = ctx->params.det_eps;
+        a.mag_thresh = ctx->params.mag_thresh;
+        if (l == 0) {
+            a.A = img1;
+            a.B = img2;
+            a.img_pitch = in_pitch;
+            a.a_pair_stride = a.b_pair_stride = in_stride;
+        } else {
+            const double* pyr = (const double*)(base + p.pyr_off[l]);
+            a.A = pyr;
+            a.B = shared ? pyr + g.img_stride : pyr + g.img_stride * n_pairs;
+            a.img_pitch = g.pitch;
+            a.a_pair_stride = a.b_pair_stride = g.img_stride;
+        }
+        if (l < L - 1) {
+            const LevelGeom& gc = p.g[l + 1];
+            a.cu = (const double*)(base + p.flow_u_off[l + 1]);
+            a.cv = (const double*)(base + p.flow_v_off[l + 1]);
+            a.c_pitch = gc.pitch;
+            a.c_pair_stride = gc.img_stride;
+            a.wc = gc.w;
+            a.hc = gc.h;
+        }
+        if (l == 0) {
+            a.u = u;
+            a.v = v;
+            a.uv_pitch = uv_step / sizeof(double);
+            a.uv_pair_stride = uv_pair_stride / sizeof(double);
+            a.mask = mask;
+            a.mask_pitch = mask_step;
+            a.mask_pair_stride = mask_pair_stride;
+            a.stats = stats;
+        } else {
+            a.u = (double*)(base + p.flow_u_off[l]);
+            a.v = (double*)(base + p.flow_v_off[l]);
+            a.uv_pitch = g.pitch;
+            a.uv_pair_stride = g.img_stride;
+        }
+        OF_CUDA(ctx, launch_lk_level(ctx, a, n_pairs, s));
+    }
+    if (stats)
+        OF_CUDA(ctx, ofb::launch_stats_finalize(stats, n_pairs, (double)ctx->params.count_thresh, s, &ctx->launches));
+    return OF_OK;
+}
+
+cudaStream_t pick(of_ctx* ctx, void* stream) { return stream ? (cudaStream_t)stream : ctx->stream; }
+
+}  // namespace
+
+extern "C" {
+
+void of_params_default(of_params* p)
+{
+    if (!p) return;
+    p->win_radius = 1;
+    p->det_eps = 0.0;
+    p->write_back_warped = 0;
+    p->mag_thresh = 20.0;
+    p->count_thresh = 500;
+}
+
+int of_abi_version(void) { return OF_B200_ABI_VERSION; }
+
+int of_get_max_layer(int width, int height)
+{
+    if (width <= 0 || height <= 0) return 0;
+    int pw = 1, ph = 1;
+    while (pw < 31 && width % (1 << pw) == 0) ++pw;
+    while (ph < 31 && height % (1 << ph) == 0) ++ph;
+    return pw < ph ? pw : ph;
+}
+
+of_status of_ctx_create(int device, const of_params* params, of_ctx** out)
+{
+    if (!out) return fail(nullptr, OF_E_BADARG, "out is NULL");
+    *out = nullptr;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0) {
+        cudaGetLastError();
+        return fail(nullptr, OF_E_CUDA, "no usable CUDA device (%s); this library has no CPU fallback",
+                    e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
+    }
+    if (device < 0 || device >= n) return fail(nullptr, OF_E_BADARG, "device %d out of range (0..%d)", device, n - 1);
+    cudaDeviceProp prop{};
+    e = cudaGetDeviceProperties(&prop, device);
+    if (e != cudaSuccess) return fail(nullptr, OF_E_CUDA, "cudaGetDeviceProperties: %s", cudaGetErrorString(e));
+    if (prop.major != 10)
+        return fail(nullptr, OF_E_CUDA, "device %d is sm_%d%d; this library is built for sm_100a (B200) only",
+                    device, prop.major, prop.minor);
+    of_ctx* ctx = new (std::nothrow) of_ctx();
+    if (!ctx) return fail(nullptr, OF_E_NOMEM, "out of host memory");
+    ctx->device = device;
+    of_params_default(&ctx->params);
+    if (params) ctx->params = *params;
+    if (const char* fv = getenv("OF_B200_VARIANT")) {
+        if (!strcmp(fv, "tile")) ctx->force_variant = 1;
+        else if (!strcmp(fv, "march")) ctx->force_variant = 2;
+    }
+    e = cudaSetDevice(device);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->down_stream, cudaStreamNonBlocking);
+    for (int i = 0; i < 2 && e == cudaSuccess; ++i) {
+        e = cudaEventCreateWithFlags(&ctx->ev_up[i], cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ctx->ev_done[i], cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ctx->ev_down[i], cudaEventDisableTiming);
+    }
+    if (e != cudaSuccess) {
+        of_status st = fail(nullptr, OF_E_CUDA, "context setup failed: %s", cudaGetErrorString(e));
+        of_ctx_destroy(ctx);
+        return st;
+    }
+    *out = ctx;
+    return OF_OK;
+}
+
+void of_ctx_destroy(of_ctx* ctx)
+{
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaDeviceSynchronize();
+    if (ctx->scratch.base) cudaFree(ctx->scratch.base);
+    if (ctx->staging.base) cudaFree(ctx->staging.base);
+    for (int i = 0; i < 2; ++i) {
+        if (ctx->ev_up[i]) cudaEventDestroy(ctx->ev_up[i]);
+        if (ctx->ev_done[i]) cudaEventDestroy(ctx->ev_done[i]);
+        if (ctx->ev_down[i]) cudaEventDestroy(ctx->ev_down[i]);
+    }
+    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
+    if (ctx->down_stream) cudaStreamDestroy(ctx->down_stream);
+    delete ctx;
+}
+
+of_status of_ctx_set_params(of_ctx* ctx, const of_params* params)
+{
+    if (!ctx || !params) return OF_E_BADARG;
+    if (params->win_radius < 1 || params->win_radius > 15) return fail(ctx, OF_E_BADARG, "win_radius must be in 1..15");
+    if (!(params->det_eps >= 0.0)) return fail(ctx, OF_E_BADARG, "det_eps must be >= 0");
+    ctx->params = *params;
+    return OF_OK;
+}
+
+const char* of_last_error_string(const of_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
+
+unsigned long long of_ctx_launch_count(const of_ctx* ctx) { return ctx ? ctx->launches : 0ull; }
+
+of_status of_ctx_synchronize(of_ctx* ctx)
+{
+    if (!ctx) return OF_E_BADARG;
+    OF_CUDA(ctx, cudaSetDevice(ctx->device));
+    OF_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    OF_CUDA(ctx, cudaStreamSynchronize(ctx->copy_stream));
+    OF_CUDA(ctx, cudaStreamSynchronize(ctx->down_stream));
+    return OF_OK;
+}
+
+of_status of_ctf_f64_batch_dev(of_ctx* ctx, int n_pairs, const double* img1, const double* img2,
+                               size_t img_pair_stride_bytes, int width, int height,
+                               size_t step_bytes, int n_levels, double* u, double* v,
+                               size_t uv_pair_stride_bytes, size_t uv_step_bytes,
+                               unsigned char* mask, size_t mask_pair_stride_bytes,
+                               size_t mask_step_bytes, of_gesture_stats* stats, void* stream)
+{
+    if (!ctx) return OF_E_BADARG;
+    return run_batch(ctx, n_pairs, img1, img2, img_pair_stride_bytes, width, height, step_bytes,
+                     n_levels, u, v, uv_pair_stride_bytes, uv_step_bytes, mask,
+                     mask_pair_stride_bytes, mask_step_bytes, stats, pick(ctx, stream));
+}
+
+of_status of_ctf_f64_dev(of_ctx* ctx, const double* img1, const double* img2, int width, int height,
+                         size_t step_bytes, int n_levels, double* u, double* v,
+                         size_t uv_step_bytes, unsigned char* mask, size_t mask_step_bytes,
+                         void* stream)
+{
+    if (!ctx) return OF_E_BADARG;
+    if (!u || !v) return fail(ctx, OF_E_BADARG, "null flow pointer");
+    return run_batch(ctx, 1, img1, img2, 0, width, height, step_bytes, n_levels, u, v, 0,
+                     uv_step_bytes, mask, 0, mask_step_bytes, nullptr, pick(ctx, stream));
+}
+
+of_status of_lk_single_f64_dev(of_ctx* ctx, const double* img1, const double* img2, int width,
+                               int height, size_t step_bytes, double* u, double* v,
+                               size_t uv_step_bytes, unsigned char* mask, size_t mask_step_bytes,
+                               void* stream)
+{
+    return of_ctf_f64_dev(ctx, img1, img2, width, height, step_bytes, 1, u, v, uv_step_bytes, mask,
+                          mask_step_bytes, stream);
+}
+
+of_status of_gesture_stats_dev(of_ctx* ctx, int n_pairs, const double* u, const double* v,
+                               size_t uv_pair_stride_bytes, int width, int height,
+                               size_t uv_step_bytes, of_gesture_stats* stats, void* stream)
+{
+    if (!ctx) return OF_E_BADARG;
+    if (!u || !v || !stats || n_pairs < 1 || width < 1 || height < 1)
+        return fail(ctx, OF_E_BADARG, "bad argument to of_gesture_stats_dev");
+    if (uv_step_bytes % 8 || uv_step_bytes < (size_t)width * 8 || uv_pair_stride_bytes % 8)
+        return fail(ctx, OF_E_BADARG, "bad step/stride");
+    OF_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t s = pick(ctx, stream);
+    OF_CUDA(ctx, cudaMemsetAsync(stats, 0, sizeof(of_gesture_stats) * n_pairs, s));
+    ofb::StatsArgs a{};
+    a.u = u;
+    a.v = v;
+    a.uv_pitch = uv_step_bytes / 8;
+    a.uv_pair_stride = uv_pair_stride_bytes / 8;
+    a.w = width;
+    a.h = height;
+    a.stats = stats;
+    a.mag_thresh = ctx->params.mag_thresh;
+    OF_CUDA(ctx, ofb::launch_gesture_stats(a, n_pairs, s, &ctx->launches));
+    OF_CUDA(ctx, ofb::launch_stats_finalize(stats, n_pairs, (double)ctx->params.count_thresh, s, &ctx->launches));
+    return OF_OK;
+}
+
+of_status of_pyr_down_f64_dev(of_ctx* ctx, const double* src, int width, int height,
+                              size_t step_bytes, double* dst, size_t dst_step_bytes, void* stream)
+{
+    if (!ctx) return OF_E_BADARG;
+    if (!src || !dst || width < 1 || height < 1) return fail(ctx, OF_E_BADARG, "bad argument to of_pyr_down_f64_dev");
+    if (step_bytes % 8 || step_bytes < (size_t)width * 8 || dst_step_bytes % 8 ||
+        dst_step_bytes < (size_t)((width + 1) / 2) * 8)
+        return fail(ctx, OF_E_BADARG, "bad step");
+    OF_CUDA(ctx, cudaSetDevice(ctx->device));
+    ofb::PyrDownArgs a{};
+    a.src = src;
+    a.src_pitch = step_bytes / 8;
+    a.dst = dst;
+    a.dst_pitch = dst_step_bytes / 8;
+    a.w = width;
+    a.h = height;
+    a.n_images = 1;
+    OF_CUDA(ctx, ofb::launch_pyr_down(a, pick(ctx, stream), &ctx->launches));
+    return OF_OK;
+}
+
+/* ---- host-pointer entry points ------------------------------------------------------- */
+
+of_status of_ctf_f64(of_ctx* ctx, double* img1, double* img2, int width, int height,
+                     size_t step_bytes, int n_levels, double* u, double* v, size_t uv_step_bytes,
+                     unsigned char* mask, size_t mask_step_bytes)
+{
+    of_status st = check_common(ctx, img1, img2, width, height, step_bytes, n_levels);
+    if (st) return st;
+    if (!u || !v) return fail(ctx, OF_E_BADARG, "null flow pointer");
+    if (uv_step_bytes % 8 || uv_step_bytes < (size_t)width * 8) return fail(ctx, OF_E_BADARG, "bad uv_step_bytes");
+    if (mask && mask_step_bytes < (size_t)width) return fail(ctx, OF_E_BADARG, "mask_step_bytes < width");
+    OF_CUDA(ctx, cudaSetDevice(ctx->device));
+    const size_t pitch = align_up((size_t)width, 16);            // doubles
+    const size_t plane = align_up(pitch * height * sizeof(double), 256);
+    const size_t mplane = align_up(pitch * height, 256);
+    st = arena_reserve(ctx, ctx->staging, 5 * plane + mplane);
+    if (st) return st;
+    char* b = ctx->staging.base;
+    double* d1 = (double*)b;
+    double* d2 = (double*)(b + plane);
+    double* du = (double*)(b + 2 * plane);
+    double* dv = (double*)(b + 3 * plane);
+    double* dw = (double*)(b + 4 * plane);
+    unsigned char* dm = (unsigned char*)(b + 5 * plane);
+    cudaStream_t s = ctx->stream;
+    const size_t rowb = (size_t)width * sizeof(double);
+    OF_CUDA(ctx, cudaMemcpy2DAsync(d1, pitch * 8, img1, step_bytes, rowb, height, cudaMemcpyHostToDevice, s));
+    OF_CUDA(ctx, cudaMemcpy2DAsync(d2, pitch * 8, img2, step_bytes, rowb, height, cudaMemcpyHostToDevice, s));
+    st = run_batch(ctx, 1, d1, d2, 0, width, height, pitch * 8, n_levels, du, dv, 0, pitch * 8,
+                   mask ? dm : nullptr, 0, pitch, nullptr, s);
+    if (st) return st;
+    OF_CUDA(ctx, cudaMemcpy2DAsync(u, uv_step_bytes, du, pitch * 8, rowb, height, cudaMemcpyDeviceToHost, s));
+    OF_CUDA(ctx, cudaMemcpy2DAsync(v, uv_step_bytes, dv, pitch * 8, rowb, height, cudaMemcpyDeviceToHost, s));
+    if (mask)
+        OF_CUDA(ctx, cudaMemcpy2DAsync(mask, mask_step_bytes, dm, pitch, (size_t)width, height, cudaMemcpyDeviceToHost, s));
+    if (ctx->params.write_back_warped && n_levels > 1) {
+        // Quirk Q1: the reference leaves the warped level-0 frames in the caller's buffers.
+        Plan p = make_plan(width, height, n_levels, 1, false);
+        ofb::WarpArgs a{};
+        a.cu = (const double*)(ctx->scratch.base + p.flow_u_off[1]);
+        a.cv = (const double*)(ctx->scratch.base + p.flow_v_off[1]);
+        a.c_pitch = p.g[1].pitch;
+        a.wc = p.g[1].w;
+        a.hc = p.g[1].h;
+        a.w = width;
+        a.h = height;
+        a.src_pitch = pitch;
+        a.dst = dw;
+        a.dst_pitch = pitch;
+        for (int k = 0; k < 2; ++k) {
+            a.src = k == 0 ? d1 : d2;
+            a.sign = k == 0 ? 1.0f : -1.0f;
+            OF_CUDA(ctx, ofb::launch_warp_level(a, s, &ctx->launches));
+            OF_CUDA(ctx, cudaMemcpy2DAsync(k == 0 ? img1 : img2, step_bytes, dw, pitch * 8, rowb, height,
+                                           cudaMemcpyDeviceToHost, s));
+        }
+    }
+    OF_CUDA(ctx, cudaStreamSynchronize(s));
+    return OF_OK;
+}
+
+of_status of_lk_single_f64(of_ctx* ctx, const double* img1, const double* img2, int width, int height,
+                           size_t step_bytes, double* u, double* v, size_t uv_step_bytes,
+                           unsigned char* mask, size_t mask_step_bytes)
+{
+    // n_levels == 1 never writes the inputs (no warp happens), so the const_cast is safe.
+    return of_ctf_f64(ctx, const_cast<double*>(img1), const_cast<double*>(img2), width, height,
+                      step_bytes, 1, u, v, uv_step_bytes, mask, mask_step_bytes);
+}
+
+of_status of_ctf_f64_stream(of_ctx* ctx, const double* frames, int n_frames, size_t frame_stride_bytes,
+                            int width, int height, size_t step_bytes, int n_levels, double* u,
+                            double* v, size_t uv_pair_stride_bytes, size_t uv_step_bytes,
+                            of_gesture_stats* stats)
+{
+    of_status st = check_common(ctx, frames, frames, width, height, step_bytes, n_levels);
+    if (st) return st;
+    if (n_frames < 2) return fail(ctx, OF_E_BADARG, "n_frames must be >= 2");
+    if ((u == nullptr) != (v == nullptr)) return fail(ctx, OF_E_BADARG, "u and v must both be given or both be NULL");
+    if (!u && !stats) return fail(ctx, OF_E_BADARG, "nothing to compute: u, v and stats are all NULL");
+    if (frame_stride_bytes % 8 || frame_stride_bytes < step_bytes * (size_t)(height - 1) + (size_t)width * 8)
+        return fail(ctx, OF_E_BADARG, "bad frame_stride_bytes");
+    if (u && (uv_step_bytes % 8 || uv_step_bytes < (size_t)width * 8 || uv_pair_stride_bytes % 8))
+        return fail(ctx, OF_E_BADARG, "bad uv step/stride");
+    OF_CUDA(ctx, cudaSetDevice(ctx->device));
+
+    const int n_pairs = n_frames - 1;
+    const size_t pitch = align_up((size_t)width, 16);
+    const size_t plane = align_up(pitch * height * sizeof(double), 256);
+    // chunk: about 256 MB of frames in flight per buffer, at most 16 pairs
+    int C = (int)(((size_t)256 << 20) / plane);
+    if (C > 16) C = 16;
+    if (C < 1) C = 1;
+    if (C > n_pairs) C = n_pairs;
+    const size_t in_bytes = plane * (C + 1);
+    const size_t out_bytes = u ? plane * C * 2 : 0;
+    const size_t st_bytes = align_up(sizeof(of_gesture_stats) * C, 256);
+    const size_t buf = in_bytes + out_bytes + st_bytes;
+    st = arena_reserve(ctx, ctx->staging, 2 * buf);
+    if (st) return st;
+    const size_t rowb = (size_t)width * sizeof(double);
+    const bool dense_in = step_bytes == rowb && pitch * 8 == rowb && frame_stride_bytes == plane;
+    const bool dense_out = u && uv_step_bytes == rowb && pitch * 8 == rowb;
+
+    const int n_chunks = (n_pairs + C - 1) / C;
+    for (int i = 0; i < n_chunks; ++i) {
+        const int bsel = i & 1;
+        char* base = ctx->staging.base + bsel * buf;
+        double* d_in = (double*)base;
+        double* d_u = (double*)(base + in_bytes);
+        double* d_v = (double*)(base + in_bytes + plane * C);
+        of_gesture_stats* d_st = (of_gesture_stats*)(base + in_bytes + out_bytes);
+        const int p0 = i * C;
+        const int np = (p0 + C <= n_pairs) ? C : n_pairs - p0;
+        // upload frames p0 .. p0+np
+        if (i >= 2) OF_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_stream, ctx->ev_done[bsel], 0));
+        const char* src = (const char*)frames + (size_t)p0 * frame_stride_bytes;
+        if (dense_in) {
+            OF_CUDA(ctx, cudaMemcpyAsync(d_in, src, plane * (np + 1), cudaMemcpyHostToDevice, ctx->copy_stream));
+        } else {
+            for (int k = 0; k <= np; ++k)
+                OF_CUDA(ctx, cudaMemcpy2DAsync((char*)d_in + k * plane, pitch * 8, src + (size_t)k * frame_stride_bytes,
+                                               step_bytes, rowb, height, cudaMemcpyHostToDevice, ctx->copy_stream));
+        }
+        OF_CUDA(ctx, cudaEventRecord(ctx->ev_up[bsel], ctx->copy_stream));
+        // compute
+        OF_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_up[bsel], 0));
+        if (i >= 2) OF_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_down[bsel], 0));
+        st = run_batch(ctx, np, d_in, (const double*)((char*)d_in + plane), plane, width, height, pitch * 8,
+                       n_levels, u ? d_u : nullptr, u ? d_v : nullptr, plane, pitch * 8, nullptr, 0, 0,
+                       stats ? d_st : nullptr, ctx->stream);
+        if (st) return st;
+        OF_CUDA(ctx, cudaEventRecord(ctx->ev_done[bsel], ctx->stream));
+        // download
+        OF_CUDA(ctx, cudaStreamWaitEvent(ctx->down_stream, ctx->ev_done[bsel], 0));
+        if (u) {
+            char* hu = (char*)u + (size_t)p0 * uv_pair_stride_bytes;
+            char* hv = (char*)v + (size_t)p0 * uv_pair_stride_bytes;
+            if (dense_out && uv_pair_stride_bytes == plane) {
+                OF_CUDA(ctx, cudaMemcpyAsync(hu, d_u, plane * np, cudaMemcpyDeviceToHost, ctx->down_stream));
+                OF_CUDA(ctx, cudaMemcpyAsync(hv, d_v, plane * np, cudaMemcpyDeviceToHost, ctx->down_stream));
+            } else {
+                for (int k = 0; k < np; ++k) {
+                    OF_CUDA(ctx, cudaMemcpy2DAsync(hu + (size_t)k * uv_pair_stride_bytes, uv_step_bytes,
+                                                   (char*)d_u + k * plane, pitch * 8, rowb, height,
+                                                   cudaMemcpyDeviceToHost, ctx->down_stream));
+                    OF_CUDA(ctx, cudaMemcpy2DAsync(hv + (size_t)k * uv_pair_stride_bytes, uv_step_bytes,
+                                                   (char*)d_v + k * plane, pitch * 8, rowb, height,
+                                                   cudaMemcpyDeviceToHost, ctx->down_stream));
+                }
+            }
+        }
+        if (stats)
+            OF_CUDA(ctx, cudaMemcpyAsync(stats + p0, d_st, sizeof(of_gesture_stats) * np, cudaMemcpyDeviceToHost,
+                                         ctx->down_stream));
+        OF_CUDA(ctx, cudaEventRecord(ctx->ev_down[bsel], ctx->down_stream));
+    }
+    OF_CUDA(ctx, cudaStreamSynchronize(ctx->copy_stream));
+    OF_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    OF_CUDA(ctx, cudaStreamSynchronize(ctx->down_stream));
+    return OF_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,83 @@
+// Host-visible launch interface of the sm_100a kernels (internal to the library; the
+// public boundary is include/of_b200.h).
+#pragma once
+#include <cuda_runtime.h>
+#include <stddef.h>
+
+#include "../../include/of_b200.h"
+
+namespace ofb {
+
+// One pyramid level of a batch of frame pairs.  Pitches and strides are in doubles
+// (mask: bytes).  Pair k uses base + k * *_pair_stride.
+struct LevelArgs {
+    const double* A;          // frame 1 at this level (unwarped pyramid level)
+    const double* B;          // frame 2 at this level
+    size_t img_pitch;
+    size_t a_pair_stride;
+    size_t b_pair_stride;
+    const double* cu;         // accumulated flow of the next-coarser level, or nullptr
+    const double* cv;
+    size_t c_pitch;
+    size_t c_pair_stride;
+    int wc, hc;               // coarse size (w/2, h/2)
+    double* u;                // accumulated flow at this level (may be nullptr: stats only)
+    double* v;
+    size_t uv_pitch;
+    size_t uv_pair_stride;
+    unsigned char* mask;      // may be nullptr
+    size_t mask_pitch;
+    size_t mask_pair_stride;
+    of_gesture_stats* stats;  // may be nullptr; accumulated with atomics (pre-zeroed)
+    double mag_thresh;
+    int w, h;
+    int radius;
+    double det_eps;
+};
+
+struct PyrDownArgs {
+    const double* src;
+    size_t src_pitch;
+    size_t src_img_stride;
+    double* dst;
+    size_t dst_pitch;
+    size_t dst_img_stride;
+    int w, h;                 // source size; destination is ((w+1)/2) x ((h+1)/2)
+    int n_images;
+};
+
+struct WarpArgs {             // write-back of the warped level (quirk Q1), optional path
+    const double* src;
+    size_t src_pitch;
+    const double* cu;
+    const double* cv;
+    size_t c_pitch;
+    int wc, hc;
+    double* dst;
+    size_t dst_pitch;
+    int w, h;
+    float sign;               // +1: frame 1 (x + f/2), -1: frame 2 (x - f/2)
+};
+
+struct StatsArgs {
+    const double* u;
+    const double* v;
+    size_t uv_pitch;
+    size_t uv_pair_stride;
+    int w, h;
+    of_gesture_stats* stats;
+    double mag_thresh;
+};
+
+// Each returns the CUDA error of the launch and adds the number of kernels it launched
+// to *launches.
+cudaError_t launch_pyr_down(const PyrDownArgs& a, cudaStream_t s, unsigned long long* launches);
+cudaError_t launch_lk_level(const LevelArgs& a, int n_pairs, cudaStream_t s,
+                            unsigned long long* launches);
+cudaError_t launch_warp_level(const WarpArgs& a, cudaStream_t s, unsigned long long* launches);
+cudaError_t launch_gesture_stats(const StatsArgs& a, int n_pairs, cudaStream_t s,
+                                 unsigned long long* launches);
+cudaError_t launch_stats_finalize(of_gesture_stats* stats, int n_pairs, double count_thresh,
+                                  cudaStream_t s, unsigned long long* launches);
+
+}  // namespace ofb

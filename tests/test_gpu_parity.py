@@ -1,0 +1,293 @@
+"""GPU suite (-m gpu): the CUDA path, called through the C ABI, against the oracle and the
+reference's golden vectors.
+
+Bars (BASELINE.json north_star / SURVEY.md 8(c)):
+  * r = 1 (the reference's window): the kernels reproduce the reference's operation order, so
+    flow is required BIT-EXACT against the FP64 oracle and <= 1e-6 against the %lf goldens
+    (the reference harness's own tolerance, ParallelBasicPyr.cpp:787,818);
+  * r > 1 (no reference summation order exists): validity mask identical, flow within
+    FLOW_TOL = 1e-3 px max-abs on valid pixels.
+"""
+import os
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN, load_gray_png
+
+pytestmark = pytest.mark.gpu
+
+FLOW_TOL = 1e-3   # px, north_star: "flow (u,v) must agree to <= 1e-3 px max-abs on valid pixels"
+
+
+@pytest.fixture(scope="module")
+def torch_cuda():
+    import torch
+    assert torch.cuda.is_available(), "GPU suite needs a CUDA device"
+    return torch
+
+
+def check(got, want, r, what=""):
+    u, v, m = got
+    uo, vo, mo = want
+    assert np.array_equal(m, mo), "%s: validity mask differs at %d pixels" % (what, (m != mo).sum())
+    if r == 1:
+        assert np.array_equal(u, uo) and np.array_equal(v, vo), \
+            "%s: r=1 must be bit-exact; max|d| = %g" % (what, max(np.abs(u - uo).max(), np.abs(v - vo).max()))
+    else:
+        err = max(np.abs(u - uo).max(), np.abs(v - vo).max())
+        assert err <= FLOW_TOL, "%s: max|dflow| = %g px" % (what, err)
+
+
+# ------------------------------------------------------------------ known-answer tests
+def test_kat1_single_level(ofb, table_pair, kat_golden, c_oracle):
+    a, b = table_pair
+    with ofb.Context(0) as ctx:
+        u, v, m = ctx.getLucasKanadeOpticalFlow(a, b, want_mask=True)
+    assert np.abs(u - kat_golden["U2Test"]).max() <= 1e-6      # serialOrig.cpp:588
+    assert np.abs(v - kat_golden["V2Test"]).max() <= 1e-6      # serialOrig.cpp:618
+    check((u, v, m), c_oracle.lk_single(a, b, want_mask=True), 1, "KAT-1")
+    assert m.sum() == (448 - 2) * (640 - 2)                     # det == 0 exactly on the ring only
+
+
+def test_kat7_pyramid(ofb, table_pair, kat_golden, c_oracle):
+    a, b = table_pair
+    L = ofb.getMaxLayer(a)
+    assert L == 7
+    with ofb.Context(0) as ctx:
+        u, v, m = ctx.coarseToFineEstimation(a, b, L, want_mask=True)
+    assert np.abs(u - kat_golden["UPyrTest"]).max() <= 1e-6    # ParallelBasicPyr.cpp:787
+    assert np.abs(v - kat_golden["VPyrTest"]).max() <= 1e-6    # ParallelBasicPyr.cpp:818
+    check((u, v, m), c_oracle.coarse_to_fine(a, b, L, want_mask=True), 1, "KAT-7")
+
+
+# ------------------------------------------------------------------ oracle sweeps
+SHAPES = [  # (H, W, L)
+    (448, 640, 3), (37, 53, 1), (2, 2, 1), (1, 9, 1), (9, 1, 1), (2, 16, 2), (16, 2, 2),
+    (64, 96, 3), (120, 200, 4), (96, 96, 6), (33, 300, 1), (300, 34, 2), (8, 8, 4),
+]
+
+
+@pytest.mark.parametrize("r", [1, 2, 3, 7])
+@pytest.mark.parametrize("shape", SHAPES)
+def test_random_inputs_vs_oracle(ofb, c_oracle, shape, r):
+    h, w, L = shape
+    rng = np.random.default_rng(h * 1000 + w + r)
+    base = rng.random((h + 8, w + 8))
+    a = base[4:4 + h, 4:4 + w].copy()
+    b = (0.7 * base[4:4 + h, 5:5 + w] + 0.3 * base[5:5 + h, 4:4 + w]) + rng.normal(0, 0.01, (h, w))
+    with ofb.Context(0, win_radius=r) as ctx:
+        got = ctx.coarseToFineEstimation(a, b, L, want_mask=True)
+    check(got, c_oracle.coarse_to_fine(a, b, L, r, want_mask=True), r, "rand %s r=%d" % (shape, r))
+
+
+@pytest.mark.parametrize("r", [1, 7])
+@pytest.mark.parametrize("L", [1, 2, 4, 5])
+def test_table_pair_levels(ofb, c_oracle, table_pair, L, r):
+    a, b = table_pair
+    with ofb.Context(0, win_radius=r) as ctx:
+        got = ctx.coarseToFineEstimation(a, b, L, want_mask=True)
+    check(got, c_oracle.coarse_to_fine(a, b, L, r, want_mask=True), r, "table L=%d r=%d" % (L, r))
+
+
+def test_roi_step_views(ofb, c_oracle, table_pair):
+    # cv::Mat ROI: step > width*8 (ParallelBasicPyr.cpp:722-723)
+    a, b = table_pair
+    ra, rb = a[10:138, 20:212], b[10:138, 20:212]
+    assert ra.strides[0] == 640 * 8
+    with ofb.Context(0) as ctx:
+        got = ctx.coarseToFineEstimation(ra, rb, 3, want_mask=True)
+    check(got, c_oracle.coarse_to_fine(ra, rb, 3, want_mask=True), 1, "ROI")
+
+
+@pytest.mark.parametrize("r", [1, 7])
+def test_exact_zero_regions_mask(ofb, c_oracle, r):
+    """Gesture-like input: large exactly-zero regions -> interior det == 0 -> flow 0
+    (cv::divide's zero rule, ParallelVideoPyr.cpp:514,518)."""
+    fr = ofb_synth().synth_frames(2, 240, 320, seed=11, gesture=True)
+    a, b = fr[0], fr[1]
+    with ofb.Context(0, win_radius=r) as ctx:
+        got = ctx.coarseToFineEstimation(a, b, 3, want_mask=True)
+    want = c_oracle.coarse_to_fine(a, b, 3, r, want_mask=True)
+    assert (~want[2]).sum() > 10000
+    check(got, want, r, "zero regions r=%d" % r)
+
+
+def test_integer_valued_inputs_like_the_live_loop(ofb, c_oracle):
+    """The live loop feeds un-normalised Sobel sums (hundreds, mostly zeros, :808-813)."""
+    rng = np.random.default_rng(2)
+    a = np.zeros((128, 160))
+    b = np.zeros((128, 160))
+    a[40:90, 30:100] = rng.integers(-400, 400, (50, 70))
+    b[42:92, 33:103] = a[40:90, 30:100]
+    for r in (1, 7):
+        with ofb.Context(0, win_radius=r) as ctx:
+            got = ctx.coarseToFineEstimation(a, b, 4, want_mask=True)
+        check(got, c_oracle.coarse_to_fine(a, b, 4, r, want_mask=True), r, "integer r=%d" % r)
+
+
+def test_det_eps_parameter(ofb, c_oracle, table_pair):
+    a, b = table_pair
+    a, b = a[:64, :96], b[:64, :96]
+    with ofb.Context(0, det_eps=1e-4) as ctx:
+        got = ctx.coarseToFineEstimation(a, b, 2, want_mask=True)
+    want = c_oracle.coarse_to_fine(a, b, 2, 1, 1e-4, want_mask=True)
+    assert 0 < want[2].sum() < want[2].size
+    check(got, want, 1, "det_eps")
+
+
+def test_identical_frames_give_zero_flow(ofb):
+    fr = ofb_synth().synth_frames(1, 270, 480, seed=5)
+    with ofb.Context(0, win_radius=7) as ctx:
+        u, v = ctx.coarseToFineEstimation(fr[0], fr[0].copy(), 3)
+    assert not u.any() and not v.any()          # ft == 0 exactly -> numerators 0 at every level
+
+
+def test_write_back_warped_quirk_q1(ofb, table_pair):
+    from oracle import lk_oracle as O
+    a, b = table_pair
+    a, b = a[:128, :160].copy(), b[:128, :160].copy()
+    tr = {}
+    uo, vo = O.coarse_to_fine(a, b, 3, trace=tr)
+    with ofb.Context(0, write_back_warped=True) as ctx:
+        u, v = ctx.coarseToFineEstimation(a, b, 3)
+    assert np.array_equal(u, uo) and np.array_equal(v, vo)
+    assert np.array_equal(a, tr[("A", 0)]) and np.array_equal(b, tr[("B", 0)])
+
+
+def test_pyr_down_primitive(ofb, c_oracle, torch_cuda):
+    torch = torch_cuda
+    rng = np.random.default_rng(9)
+    with ofb.Context(0) as ctx:
+        for (h, w) in [(7, 10), (1, 9), (9, 1), (2, 2), (31, 17), (270, 480), (135, 240)]:
+            x = rng.standard_normal((h, w))
+            src = torch.from_numpy(x).cuda()
+            dst = torch.empty(((h + 1) // 2, (w + 1) // 2), dtype=torch.float64, device="cuda")
+            ctx.pyr_down_dev(src, dst)
+            torch.cuda.synchronize()
+            assert np.array_equal(dst.cpu().numpy(), c_oracle.pyr_down(x)), (h, w)
+
+
+# ------------------------------------------------------------------ errors
+def test_error_codes(ofb):
+    z = np.zeros((30, 40))
+    with ofb.Context(0) as ctx:
+        with pytest.raises(ofb.NotDivisibleError):
+            ctx.coarseToFineEstimation(z, z, 3)              # 30 % 4 != 0 (Q2, :635 throws)
+        with pytest.raises(ofb.BadArgError):
+            ctx.coarseToFineEstimation(z, np.zeros((30, 41)), 1)
+        with pytest.raises(ofb.BadArgError):
+            ctx.coarseToFineEstimation(z, z, 0)
+        with pytest.raises(ofb.BadArgError):
+            ctx.set_params(win_radius=0)
+        u, v = ctx.coarseToFineEstimation(z, z, 2)           # still usable after errors
+        assert not u.any()
+
+
+# ------------------------------------------------------------------ device / batch / stream
+def test_device_and_batch_entry_points(ofb, c_oracle, torch_cuda):
+    torch = torch_cuda
+    fr = ofb_synth().synth_frames(5, 96, 160, seed=3)
+    d = torch.from_numpy(fr).cuda()
+    for r in (1, 7):
+        want = [c_oracle.coarse_to_fine(fr[k], fr[k + 1], 3, r, want_mask=True) for k in range(4)]
+        with ofb.Context(0, win_radius=r, mag_thresh=0.5, count_thresh=100) as ctx:
+            # single-pair device call on torch's current stream
+            u = torch.empty((96, 160), dtype=torch.float64, device="cuda")
+            v = torch.empty_like(u)
+            m = torch.empty((96, 160), dtype=torch.uint8, device="cuda")
+            ctx.coarseToFineEstimation_dev(d[0], d[1], 3, u, v, m)
+            torch.cuda.synchronize()
+            check((u.cpu().numpy(), v.cpu().numpy(), m.cpu().numpy().astype(bool)), want[0], r, "dev")
+            # consecutive-pair batch (shared pyramids) + stats + mask
+            U = torch.empty((4, 96, 160), dtype=torch.float64, device="cuda")
+            V = torch.empty_like(U)
+            M = torch.empty((4, 96, 160), dtype=torch.uint8, device="cuda")
+            S = torch.empty((4, 4), dtype=torch.float64, device="cuda")
+            assert ctx.flow_batch_dev(d, 3, U, V, S, M) == 4
+            torch.cuda.synchronize()
+            for k in range(4):
+                got = (U[k].cpu().numpy(), V[k].cpu().numpy(), M[k].cpu().numpy().astype(bool))
+                check(got, want[k], r, "batch pair %d" % k)
+                s = c_oracle.gesture_stats(got[0], got[1], 0.5, 100)
+                row = S[k].cpu().numpy()
+                assert (row[0], row[1], row[2], bool(row[3])) == (s["sum_x"], s["sum_y"], s["count"], s["detected"])
+            # split pairing (independent pairs, separate pyramids): frames [0,1 | 2,3] -> (0,2), (1,3)
+            U2 = torch.empty((2, 96, 160), dtype=torch.float64, device="cuda")
+            V2 = torch.empty_like(U2)
+            ctx.flow_batch_dev(d[:4].contiguous(), 3, U2, V2, pairs="split")
+            # stats-only call and stand-alone stats kernel
+            S2 = torch.empty((4, 4), dtype=torch.float64, device="cuda")
+            ctx.flow_batch_dev(d, 3, None, None, S2)
+            S3 = torch.empty((4, 4), dtype=torch.float64, device="cuda")
+            ctx.gesture_stats_dev(U, V, S3)
+            torch.cuda.synchronize()
+            assert torch.equal(S, S2) and torch.equal(S, S3)
+            for j, (ka, kb) in enumerate(((0, 2), (1, 3))):
+                wo = c_oracle.coarse_to_fine(fr[ka], fr[kb], 3, r)
+                err = max(np.abs(U2[j].cpu().numpy() - wo[0]).max(), np.abs(V2[j].cpu().numpy() - wo[1]).max())
+                assert err <= (0.0 if r == 1 else FLOW_TOL)
+
+
+def test_host_stream_entry_point_pacman(ofb, c_oracle):
+    """BASELINE config 2: every consecutive pair of pacman.mp4 (195 decodable frames,
+    240x160, L = getMaxLayer = 5), one GPU, through the host-pointer stream call."""
+    fr = np.load(os.path.join(GOLDEN, "pacman_gray.npz"))["frames"].astype(np.float64) / 255.0
+    assert fr.shape == (195, 160, 240)
+    L = ofb.getMaxLayer(240, 160)
+    assert L == 5
+    with ofb.Context(0, mag_thresh=1.0, count_thresh=50) as ctx:
+        U, V, S = ctx.flow_stream(fr, L)
+    assert U.shape == (194, 160, 240)
+    for k in range(194):
+        uo, vo = c_oracle.coarse_to_fine(fr[k], fr[k + 1], L)
+        assert np.array_equal(U[k], uo) and np.array_equal(V[k], vo), "pair %d" % k
+        s = c_oracle.gesture_stats(uo, vo, 1.0, 50)
+        assert (S["sum_x"][k], S["sum_y"][k], S["count"][k]) == (s["sum_x"], s["sum_y"], s["count"])
+        assert bool(S["detected"][k]) == s["detected"]
+
+
+def test_hand_pair_config0(ofb, c_oracle):
+    """BASELINE config 0: hand1 -> hand2 (3264x2448, EXIF ignored as OpenCV 2.4 did),
+    L = getMaxLayer = 5, the reference's 3x3 window."""
+    a = load_gray_png("hand1_gray.png").astype(np.float64) / 255.0
+    b = load_gray_png("hand2_gray.png").astype(np.float64) / 255.0
+    assert a.shape == (2448, 3264)
+    L = ofb.getMaxLayer(a)
+    assert L == 5
+    with ofb.Context(0) as ctx:
+        got = ctx.coarseToFineEstimation(a, b, L, want_mask=True)
+    check(got, c_oracle.coarse_to_fine(a, b, L, want_mask=True), 1, "hand pair")
+
+
+@pytest.mark.parametrize("cfg", [(1080, 1920, 3, 7), (1080, 1920, 3, 1), (1080, 1080, 4, 1), (2160, 3840, 4, 7)])
+def test_full_size_configs(ofb, c_oracle, torch_cuda, cfg):
+    """BASELINE configs 3/4 at full size: one pair against the C oracle, plus size-independent
+    properties: batch == single, determinism, finite output."""
+    torch = torch_cuda
+    h, w, L, r = cfg
+    fr = ofb_synth().synth_frames(3, h, w, seed=1234)
+    d = torch.from_numpy(fr).cuda()
+    with ofb.Context(0, win_radius=r) as ctx:
+        U = torch.empty((2, h, w), dtype=torch.float64, device="cuda")
+        V = torch.empty_like(U)
+        M = torch.empty((2, h, w), dtype=torch.uint8, device="cuda")
+        ctx.flow_batch_dev(d, L, U, V, None, M)
+        u1 = torch.empty((h, w), dtype=torch.float64, device="cuda")
+        v1 = torch.empty_like(u1)
+        ctx.coarseToFineEstimation_dev(d[1], d[2], L, u1, v1)
+        U_again = torch.empty_like(U)
+        V_again = torch.empty_like(V)
+        ctx.flow_batch_dev(d, L, U_again, V_again)
+        torch.cuda.synchronize()
+    assert torch.isfinite(U).all() and torch.isfinite(V).all()
+    assert torch.equal(U[1], u1) and torch.equal(V[1], v1)            # batch == single
+    assert torch.equal(U, U_again) and torch.equal(V, V_again)        # deterministic
+    want = c_oracle.coarse_to_fine(fr[0], fr[1], L, r, want_mask=True)
+    check((U[0].cpu().numpy(), V[0].cpu().numpy(), M[0].cpu().numpy().astype(bool)), want, r, "full %s" % (cfg,))
+
+
+def ofb_synth():
+    import importlib
+    from of_b200_loader import ofb  # noqa: F401  (registers the package)
+    return importlib.import_module("optical_flow_b200.synth")
