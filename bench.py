@@ -1,0 +1,343 @@
+#!/usr/bin/env python
+"""Benchmark of the dense pyramidal Lucas-Kanade path (BASELINE.json metric).
+
+    python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path
+    python bench.py --impl reference --gpus N --steps K ...  # CPU baseline arm
+
+Workload (BASELINE.json configs[3], the configuration the metric is quoted on): synthetic
+1920x1080 grayscale video, 3-level pyramid, 15x15 window (r = 7), FP64.  One "step" = one batch
+of PAIRS consecutive frame pairs (PAIRS+1 frames) through of_ctf_f64_batch_dev with inputs and
+outputs resident in HBM.  Each step touches (PAIRS+1)*16.6 MB of frames and PAIRS*33.2 MB of
+flow, far more than the 126 MB L2, so no explicit L2 flush is needed between steps.
+
+value  = frame pairs per second, whole job (all ranks), device-resident, CUDA-event timed,
+         max over ranks.
+e2e    = the same metric through the host-pointer stream call (of_ctf_f64_stream): frames in
+         pinned host memory, flow fields read back to pinned host memory, copies inside the
+         timed region.
+roofline = the level-0 fused kernel (dominant): algorithmic bytes per launch (36 B per level-0
+         pixel per pair: read A,B 16 + write u,v 16 + coarse flow 4) / its average launch
+         duration measured with CUDA events on the launching stream inside the timed region.
+cpu_baseline = the C+OpenMP oracle port of the reference's path on the host cores, bounded
+         sample, rank 0, N = 1 only.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+W, H, LEVELS, RADIUS = 1920, 1080, 3, 7
+PAIRS = 16                      # frame pairs per step per GPU
+METRIC = "frame_pairs_per_sec_1080p_3level_lk"
+UNIT = "pairs/s"
+
+
+def level_sizes(w, h, L):
+    return [(w >> l) * (h >> l) for l in range(L)]
+
+
+def algorithmic_bytes_per_pair(w, h, L):
+    """pyramid 16*(sum_{l<L-1} N_l + sum_{l>=1} N_l) + per level 32*N_l (+16*N_{l+1})."""
+    n = level_sizes(w, h, L)
+    pyr = 16 * (sum(n[:-1]) + sum(n[1:]))
+    lev = sum(32 * n[l] + (16 * n[l + 1] if l < L - 1 else 0) for l in range(L))
+    return pyr + lev
+
+
+def level0_bytes_per_pair(w, h, L):
+    n = level_sizes(w, h, L)
+    return 32 * n[0] + (16 * n[1] if L > 1 else 0)
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured"
+        except Exception:
+            pass
+    return 6650.0, "fallback"
+
+
+class ClockSampler:
+    """Samples nvidia-smi clocks and throttle reasons during the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index
+        self.rows = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            f = [x.strip() for x in r.split(",")]
+            if len(f) < 6:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for nm, val in zip(names, f[2:6]):
+                if val.lower().startswith("active"):
+                    reasons.add(nm)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def synth(n_frames, seed=1234):
+    import importlib
+    from of_b200_loader import ofb  # noqa: F401
+    return importlib.import_module("optical_flow_b200.synth").synth_frames(n_frames, H, W, seed=seed)
+
+
+def cpu_baseline_run(frames, n_pairs, repeats=1):
+    """Times the C+OpenMP oracle port (oracle/lk_oracle.c) on n_pairs pairs of the workload,
+    all host threads.  Returns (pairs_per_s, cores, seconds)."""
+    from oracle import c_oracle as CO
+    CO.build()
+    cores = os.cpu_count() or 1
+    CO.coarse_to_fine(frames[0][:64, :64].copy(), frames[1][:64, :64].copy(), 1, 1)   # thread-pool warm-up
+    t0 = time.perf_counter()
+    done = 0
+    for _ in range(repeats):
+        for k in range(n_pairs):
+            CO.coarse_to_fine(frames[k % (len(frames) - 1)], frames[k % (len(frames) - 1) + 1], LEVELS, RADIUS)
+            done += 1
+    dt = time.perf_counter() - t0
+    return done / dt, cores, dt
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU implementation of the path.  The reference itself
+    (OpenCV 2.4 C++) cannot be compiled in this image, so this times the oracle port of it
+    (oracle/lk_oracle.c, C + OpenMP, every host thread) on the same workload; one step = a
+    bounded sample of SAMPLE pairs."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    sample = 2
+    frames = synth(sample + 1)
+    from oracle import c_oracle as CO
+    CO.build()
+    cores = os.cpu_count() or 1
+    for _ in range(max(args.warmup, 1)):
+        CO.coarse_to_fine(frames[0], frames[1], LEVELS, RADIUS)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        for k in range(sample):
+            CO.coarse_to_fine(frames[k], frames[k + 1], LEVELS, RADIUS)
+    dt = time.perf_counter() - t0
+    val = args.steps * sample / dt
+    line = {
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic",
+        "config": {"workload": "synthetic 1920x1080 video, 3-level pyramid, 15x15 window (r=7), %d pairs per step" % sample,
+                   "width": W, "height": H, "levels": LEVELS, "win_radius": RADIUS},
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port",
+                         "sample": "%d steps x %d consecutive pairs of the synthetic 1080p stream, "
+                                   "oracle/lk_oracle.c (gcc -O3 -fopenmp), all host threads" % (args.steps, sample)},
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def run_ours(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from of_b200_loader import ofb
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; this path has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    pairs = args.pairs
+    radius = args.radius
+
+    frames_h = synth(pairs + 1, seed=1234 + rank)             # each rank: its own stream segment (weak scaling)
+    frames = torch.from_numpy(frames_h).to(dev)
+    U = torch.empty((pairs, H, W), dtype=torch.float64, device=dev)
+    V = torch.empty_like(U)
+    S = torch.zeros((pairs, 4), dtype=torch.float64, device=dev)
+    ctx = ofb.Context(local_rank, win_radius=radius)
+    import importlib
+    shard = importlib.import_module("optical_flow_b200.shard")
+    counts = [pairs] * world
+
+    def step():
+        ctx.flow_batch_dev(frames, LEVELS, U, V, S)
+        if world > 1:                                         # the path's only exchange: stats to rank 0
+            shard.gather_to_rank0(S, counts)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    barrier()
+
+    # ---- device-resident timed region ------------------------------------------------------
+    ctx.set_timing(True)
+    lvl0_ms, lvl_ms, pyr_ms = [], [], []
+    sampler = ClockSampler(torch.cuda.current_device() if os.environ.get("CUDA_VISIBLE_DEVICES") is None else local_rank)
+    launches0 = ctx.launch_count
+    e0 = torch.cuda.Event(enable_timing=True)
+    e1 = torch.cuda.Event(enable_timing=True)
+    barrier()
+    sampler.start()
+    e0.record()
+    for i in range(args.steps):
+        step()
+    e1.record()
+    barrier()
+    clocks = sampler.stop()
+    ms_total = e0.elapsed_time(e1)
+    # per-launch durations of every kernel launched inside the timed region (events on the
+    # launching stream, recorded by the library around each launch)
+    for kind, level, ms in ctx.get_timing():
+        if kind == 1 and level == 0:
+            lvl0_ms.append(ms)
+        elif kind == 1:
+            lvl_ms.append(ms)
+        else:
+            pyr_ms.append(ms)
+    ctx.set_timing(False)
+    launches = ctx.launch_count - launches0
+    t = torch.tensor([ms_total], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_total = float(t.item())
+    value = world * pairs * args.steps / (ms_total * 1e-3)
+
+    # ---- end-to-end through the host-pointer stream call --------------------------------------
+    host_in = torch.empty((pairs + 1, H, W), dtype=torch.float64).pin_memory()
+    host_in.copy_(torch.from_numpy(frames_h))
+    host_u = torch.empty((pairs, H, W), dtype=torch.float64).pin_memory()
+    host_v = torch.empty((pairs, H, W), dtype=torch.float64).pin_memory()
+    e2e_steps = max(2, min(args.steps, 10))
+    fin, hu, hv = host_in.numpy(), host_u.numpy(), host_v.numpy()
+    ctx.flow_stream(fin, LEVELS, out_u=hu, out_v=hv)          # warm-up (allocates staging)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        ctx.flow_stream(fin, LEVELS, out_u=hu, out_v=hv)
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    t = torch.tensor([dt], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_val = world * pairs * e2e_steps / float(t.item())
+    frame_bytes = H * W * 8
+
+    if rank == 0:
+        peak, peak_src = measured_peaks()
+        l0 = sum(lvl0_ms) / len(lvl0_ms) if lvl0_ms else None
+        roof = None
+        if l0:
+            achieved = level0_bytes_per_pair(W, H, LEVELS) * pairs / (l0 * 1e-3) / 1e9
+            traffic = None
+            tp = os.path.join(ROOT, "profiles", "traffic.json")
+            if os.path.exists(tp):
+                try:
+                    traffic = json.load(open(tp)).get("level0_r%d_bytes_per_launch" % radius)
+                except Exception:
+                    traffic = None
+            roof = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                    "traffic": traffic, "peak_source": peak_src, "kernel": "lk_level (level 0, fused)",
+                    "launch_ms": l0, "algorithmic_bytes_per_launch": level0_bytes_per_pair(W, H, LEVELS) * pairs,
+                    "whole_path_frac": algorithmic_bytes_per_pair(W, H, LEVELS) * (value / world) / (peak * 1e9),
+                    "kernel_ms_per_step": {"level0": l0, "coarser_levels": sum(lvl_ms) / args.steps,
+                                           "pyr_down": sum(pyr_ms) / args.steps}}
+        cpu = None
+        if world == 1 and not args.no_cpu_baseline:
+            v, cores, secs = cpu_baseline_run(frames_h, 3)
+            cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
+                   "sample": "3 consecutive pairs of the same synthetic 1080p stream (L=3, r=%d), oracle/lk_oracle.c "
+                             "C+OpenMP port of the reference path, all host threads, %.1f s" % (RADIUS, secs)}
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms_total / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": "synthetic 1920x1080 grayscale video, 3-level pyramid, 15x15 window (r=%d), "
+                                   "%d consecutive frame pairs per step per GPU" % (radius, pairs),
+                       "width": W, "height": H, "levels": LEVELS, "win_radius": radius, "pairs_per_step": pairs,
+                       "l2": "inputs+outputs per step (%.0f MB) exceed the 126 MB L2; no flush" %
+                             (((pairs + 1) + 2 * pairs) * frame_bytes / 1e6),
+                       "exchange": "per-step gather of gesture statistics (32 B/pair) to rank 0" if world > 1 else "none"},
+            "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": (pairs + 1) * frame_bytes,
+                    "d2h_bytes_per_step": 2 * pairs * frame_bytes, "steps": e2e_steps,
+                    "api": "of_ctf_f64_stream (pinned host frames in, full u/v flow fields out)"},
+            "gpu_launches": int(launches),
+            "clocks": clocks,
+            "roofline": roof,
+            "cpu_baseline": cpu,
+        }
+        print(json.dumps(line), flush=True)
+    ctx.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--pairs", type=int, default=PAIRS)
+    ap.add_argument("--radius", type=int, default=RADIUS)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

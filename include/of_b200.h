@@ -159,6 +159,14 @@ OF_API of_status of_pyr_down_f64_dev(of_ctx *ctx, const double *src, int width, 
 /* Blocks until everything queued on the context's own stream has finished. */
 OF_API of_status of_ctx_synchronize(of_ctx *ctx);
 
+/* Per-launch device timing (bench roofline evidence).  When enabled, every kernel of a batch
+ * call is bracketed by CUDA events on the launching stream (up to 8192 launches since the last
+ * of_ctx_set_timing call).  of_ctx_get_timing returns, for those launches in order, kinds[i] (0 = pyrDown producing level levels[i], 1 = fused level
+ * kernel of level levels[i]) and the device duration ms[i]; it waits for those events. */
+OF_API of_status of_ctx_set_timing(of_ctx *ctx, int enable);
+OF_API of_status of_ctx_get_timing(of_ctx *ctx, int max_entries, int *kinds, int *levels,
+                                   float *ms, int *n);
+
 /* Number of kernel launches issued through this context since creation (bench evidence). */
 OF_API unsigned long long of_ctx_launch_count(const of_ctx *ctx);
 

@@ -28,7 +28,7 @@ EXPORTS = (
     "of_ctx_set_params", "of_last_error_string", "of_abi_version", "of_lk_single_f64",
     "of_ctf_f64", "of_ctf_f64_stream", "of_lk_single_f64_dev", "of_ctf_f64_dev",
     "of_ctf_f64_batch_dev", "of_gesture_stats_dev", "of_pyr_down_f64_dev",
-    "of_ctx_synchronize", "of_ctx_launch_count",
+    "of_ctx_synchronize", "of_ctx_launch_count", "of_ctx_set_timing", "of_ctx_get_timing",
 )
 
 
@@ -95,6 +95,8 @@ def lib():
     L.of_ctx_synchronize.argtypes = [vp]
     L.of_ctx_launch_count.argtypes = [vp]
     L.of_ctx_launch_count.restype = C.c_ulonglong
+    L.of_ctx_set_timing.argtypes = [vp, ci]
+    L.of_ctx_get_timing.argtypes = [vp, ci, vp, vp, vp, vp]
     _ = dbl
     _lib = L
     return L
@@ -123,6 +125,15 @@ def _np_f64_2d(a, name):
     if a.strides[1] != 8 or a.strides[0] < a.shape[1] * 8 or a.strides[0] % 8:
         a = np.ascontiguousarray(a)
     return a
+
+
+def _stream_handle(stream, device):
+    """cudaStream_t of a torch stream for the C ABI.  torch's default stream has handle 0,
+    which the ABI reads as "the context's own stream", so it is passed as cudaStreamLegacy
+    (0x1) -- the same stream, named explicitly."""
+    import torch
+    h = (stream or torch.cuda.current_stream(device)).cuda_stream
+    return h if h else 1
 
 
 class Context:
@@ -183,6 +194,20 @@ class Context:
 
     def synchronize(self):
         self._check(lib().of_ctx_synchronize(self._h))
+
+    def set_timing(self, enable: bool):
+        self._check(lib().of_ctx_set_timing(self._h, int(bool(enable))))
+
+    def get_timing(self):
+        """[(kind, level, ms)] of every launch since set_timing(True) (at most 8192);
+        kind 0 = pyrDown producing `level`, 1 = fused level kernel."""
+        n = C.c_int(0)
+        cap = 8192
+        kinds = (C.c_int * cap)()
+        levels = (C.c_int * cap)()
+        ms = (C.c_float * cap)()
+        self._check(lib().of_ctx_get_timing(self._h, cap, kinds, levels, ms, C.byref(n)))
+        return [(kinds[i], levels[i], ms[i]) for i in range(n.value)]
 
     # -- host-pointer calls (numpy) -----------------------------------------------------
     def getLucasKanadeOpticalFlow(self, img1, img2, want_mask: bool = False):
@@ -259,7 +284,7 @@ class Context:
                 or u.stride(0) != v.stride(0):
             raise BadArgError(OF_E_BADARG, "shape/stride mismatch")
         h, w = a.shape
-        s = (stream or torch.cuda.current_stream(a.device)).cuda_stream
+        s = _stream_handle(stream, a.device)
         st = lib().of_ctf_f64_dev(self._h, a.data_ptr(), b.data_ptr(), w, h, a.stride(0) * 8, int(nLevels),
                                   u.data_ptr(), v.data_ptr(), u.stride(0) * 8,
                                   mask.data_ptr() if mask is not None else None,
@@ -297,7 +322,7 @@ class Context:
         if mask is not None and (mask.dtype != torch.uint8 or tuple(mask.shape) != (npairs, h, w)
                                  or not mask.is_contiguous()):
             raise BadArgError(OF_E_BADARG, "mask must be a contiguous (n_pairs, H, W) uint8 CUDA tensor")
-        s = (stream or torch.cuda.current_stream(f.device)).cuda_stream
+        s = _stream_handle(stream, f.device)
         st = lib().of_ctf_f64_batch_dev(
             self._h, npairs, p1, p2, fb, w, h, w * 8, int(nLevels),
             u.data_ptr() if u is not None else None, v.data_ptr() if v is not None else None, fb, w * 8,
@@ -309,13 +334,13 @@ class Context:
     def gesture_stats_dev(self, u, v, stats, stream=None):
         import torch
         npairs, h, w = u.shape
-        s = (stream or torch.cuda.current_stream(u.device)).cuda_stream
+        s = _stream_handle(stream, u.device)
         self._check(lib().of_gesture_stats_dev(self._h, npairs, u.data_ptr(), v.data_ptr(), h * w * 8,
                                                w, h, w * 8, stats.data_ptr(), s))
 
     def pyr_down_dev(self, src, dst, stream=None):
         import torch
         h, w = src.shape
-        s = (stream or torch.cuda.current_stream(src.device)).cuda_stream
+        s = _stream_handle(stream, src.device)
         self._check(lib().of_pyr_down_f64_dev(self._h, src.data_ptr(), w, h, src.stride(0) * 8,
                                               dst.data_ptr(), dst.stride(0) * 8, s))

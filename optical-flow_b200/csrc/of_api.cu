@@ -49,6 +49,11 @@ struct of_ctx {
     std::string err;
     unsigned long long launches = 0;
     int force_variant = 0;             // 0 auto, 1 tile, 2 march (test hook via OF_B200_VARIANT)
+    // optional per-launch device timing of the most recent batch call (bench roofline evidence)
+    bool timing = false;
+    std::vector<cudaEvent_t> tev;      // 2 events per timed launch
+    std::vector<int> tkind, tlevel;
+    size_t tcount = 0;
 };
 
 namespace {
@@ -157,6 +162,35 @@ of_status check_common(of_ctx* ctx, const void* a, const void* b, int w, int h, 
     return OF_OK;
 }
 
+// Brackets one kernel launch with events on the launching stream when timing is enabled.
+struct TimedLaunch {
+    of_ctx* ctx;
+    cudaStream_t s;
+    bool on;
+    TimedLaunch(of_ctx* c, cudaStream_t st, int kind, int level) : ctx(c), s(st), on(c->timing)
+    {
+        if (!on) return;
+        if (ctx->tcount >= 8192) { on = false; return; }
+        if (ctx->tev.size() < 2 * (ctx->tcount + 1)) {
+            cudaEvent_t e0 = nullptr, e1 = nullptr;
+            if (cudaEventCreate(&e0) != cudaSuccess || cudaEventCreate(&e1) != cudaSuccess) { on = false; return; }
+            ctx->tev.push_back(e0);
+            ctx->tev.push_back(e1);
+            ctx->tkind.push_back(0);
+            ctx->tlevel.push_back(0);
+        }
+        ctx->tkind[ctx->tcount] = kind;
+        ctx->tlevel[ctx->tcount] = level;
+        cudaEventRecord(ctx->tev[2 * ctx->tcount], s);
+    }
+    ~TimedLaunch()
+    {
+        if (!on) return;
+        cudaEventRecord(ctx->tev[2 * ctx->tcount + 1], s);
+        ctx->tcount += 1;
+    }
+};
+
 cudaError_t launch_lk_level(of_ctx* ctx, const ofb::LevelArgs& a, int n_pairs, cudaStream_t s)
 {
     if (ctx->force_variant != 1) {
@@ -214,11 +248,16 @@ of_status run_batch(of_ctx* ctx, int n_pairs, const double* img1, const double* 
             a.src_img_stride = in_stride;
             if (shared) {
                 a.src = img1; a.dst = dst; a.n_images = n_pairs + 1;
+                TimedLaunch t(ctx, s, 0, l);
                 OF_CUDA(ctx, ofb::launch_pyr_down(a, s, &ctx->launches));
             } else {
                 a.src = img1; a.dst = dst; a.n_images = n_pairs;
-                OF_CUDA(ctx, ofb::launch_pyr_down(a, s, &ctx->launches));
+                {
+                    TimedLaunch t(ctx, s, 0, l);
+                    OF_CUDA(ctx, ofb::launch_pyr_down(a, s, &ctx->launches));
+                }
                 a.src = img2; a.dst = dst + gd.img_stride * n_pairs;
+                TimedLaunch t(ctx, s, 0, l);
                 OF_CUDA(ctx, ofb::launch_pyr_down(a, s, &ctx->launches));
             }
         } else {
@@ -227,6 +266,7 @@ of_status run_batch(of_ctx* ctx, int n_pairs, const double* img1, const double* 
             a.src_img_stride = gs.img_stride;
             a.dst = dst;
             a.n_images = p.n_frames;
+            TimedLaunch t(ctx, s, 0, l);
             OF_CUDA(ctx, ofb::launch_pyr_down(a, s, &ctx->launches));
         }
     }
@@ -278,6 +318,7 @@ of_status run_batch(of_ctx* ctx, int n_pairs, const double* img1, const double* 
             a.uv_pitch = g.pitch;
             a.uv_pair_stride = g.img_stride;
         }
+        TimedLaunch t(ctx, s, 1, l);
         OF_CUDA(ctx, launch_lk_level(ctx, a, n_pairs, s));
     }
     if (stats)
@@ -364,6 +405,7 @@ void of_ctx_destroy(of_ctx* ctx)
     cudaDeviceSynchronize();
     if (ctx->scratch.base) cudaFree(ctx->scratch.base);
     if (ctx->staging.base) cudaFree(ctx->staging.base);
+    for (cudaEvent_t e : ctx->tev) cudaEventDestroy(e);
     for (int i = 0; i < 2; ++i) {
         if (ctx->ev_up[i]) cudaEventDestroy(ctx->ev_up[i]);
         if (ctx->ev_done[i]) cudaEventDestroy(ctx->ev_done[i]);
@@ -387,6 +429,29 @@ of_status of_ctx_set_params(of_ctx* ctx, const of_params* params)
 const char* of_last_error_string(const of_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
 
 unsigned long long of_ctx_launch_count(const of_ctx* ctx) { return ctx ? ctx->launches : 0ull; }
+
+of_status of_ctx_set_timing(of_ctx* ctx, int enable)
+{
+    if (!ctx) return OF_E_BADARG;
+    ctx->timing = enable != 0;
+    ctx->tcount = 0;
+    return OF_OK;
+}
+
+of_status of_ctx_get_timing(of_ctx* ctx, int max_entries, int* kinds, int* levels, float* ms, int* n)
+{
+    if (!ctx || !n || (max_entries > 0 && (!kinds || !levels || !ms))) return OF_E_BADARG;
+    OF_CUDA(ctx, cudaSetDevice(ctx->device));
+    int cnt = 0;
+    for (size_t i = 0; i < ctx->tcount && cnt < max_entries; ++i, ++cnt) {
+        OF_CUDA(ctx, cudaEventSynchronize(ctx->tev[2 * i + 1]));
+        OF_CUDA(ctx, cudaEventElapsedTime(&ms[cnt], ctx->tev[2 * i], ctx->tev[2 * i + 1]));
+        kinds[cnt] = ctx->tkind[i];
+        levels[cnt] = ctx->tlevel[i];
+    }
+    *n = cnt;
+    return OF_OK;
+}
 
 of_status of_ctx_synchronize(of_ctx* ctx)
 {
