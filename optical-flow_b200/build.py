@@ -23,7 +23,7 @@ NVCC_FLAGS = [
     "-Xcompiler", "-fPIC",
     "-Xcompiler", "-fvisibility=hidden",
     "-cudart", "static",
-    "-DOF_B200_BUILD",
+    "-DOF_B200_BUILD", "-diag-suppress", "177",
 ]
 
 

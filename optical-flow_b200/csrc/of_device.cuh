@@ -77,6 +77,14 @@ __device__ __forceinline__ void q5(float m, int& ip, int& frac)
     frac = s & 31;
 }
 
+// k / 1024 for an integer 0 <= k <= 1024, exactly, with one FP64 add instead of an
+// int->double conversion (conversions issue at 1/4 of the DADD rate on sm_100):
+// the double with high word 0x42900000 and low word k is 2^42 + k * 2^-10.
+__device__ __forceinline__ double q10_to_double(int k)
+{
+    return __dsub_rn(__hiloint2double(0x42900000, k), 4398046511104.0);
+}
+
 // Bilinear sample of `src` (w x h, row pitch `pitch` doubles) at map coordinate (mx, my):
 // float32 weights (exact multiples of 1/1024), double blend left to right,
 // BORDER_CONSTANT 0 tested per tap.
@@ -86,10 +94,10 @@ __device__ __forceinline__ double remap_tap4(const double* __restrict__ src, siz
     int ix, iy, ax, ay;
     q5(mx, ix, ax);
     q5(my, iy, ay);
-    const double w00 = (double)((32 - ay) * (32 - ax)) * (1.0 / 1024.0);
-    const double w01 = (double)((32 - ay) * ax) * (1.0 / 1024.0);
-    const double w10 = (double)(ay * (32 - ax)) * (1.0 / 1024.0);
-    const double w11 = (double)(ay * ax) * (1.0 / 1024.0);
+    const double w00 = q10_to_double((32 - ay) * (32 - ax));
+    const double w01 = q10_to_double((32 - ay) * ax);
+    const double w10 = q10_to_double(ay * (32 - ax));
+    const double w11 = q10_to_double(ay * ax);
     const bool x0 = (unsigned)ix < (unsigned)w, x1 = (unsigned)(ix + 1) < (unsigned)w;
     const bool y0 = (unsigned)iy < (unsigned)h, y1 = (unsigned)(iy + 1) < (unsigned)h;
     const double* p = src + (ptrdiff_t)iy * (ptrdiff_t)pitch + ix;
@@ -105,7 +113,7 @@ __device__ __forceinline__ void map_coords(int x, int y, double upu, double upv,
                                            float& m1x, float& m1y, float& m2x, float& m2y)
 {
     const float fu = __double2float_rn(upu), fv = __double2float_rn(upv);
-    const float hu = __fdiv_rn(fu, 2.0f), hv = __fdiv_rn(fv, 2.0f);
+    const float hu = __fmul_rn(fu, 0.5f), hv = __fmul_rn(fv, 0.5f);   // == f / 2 exactly
     m1x = __fadd_rn((float)x, hu);
     m1y = __fadd_rn((float)y, hv);
     m2x = __fsub_rn((float)x, hu);
