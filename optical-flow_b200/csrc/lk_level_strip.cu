@@ -1,0 +1,859 @@
+// Strip-marching fused pyramid-level kernel, V3 (throughput path), window radius R = 2..7.
+//
+// One launch = one pyramid level of every pair of the batch, everything the reference does
+// between two levels (ParallelVideoPyr.cpp:610-703) plus the single-level LK (:327-542):
+//   pyrUp(coarse flow) -> float32 maps -> remap of both frames -> fx/fy/ft -> products ->
+//   (2R+1)^2 window sums -> guarded 2x2 solve -> += upsampled coarse flow.
+//
+// A CTA (4 warps) owns a strip of OUT_COLS output columns and marches down a chunk of rows:
+//
+//   producers (warps 0,1; lane = 4 consecutive columns; warp p takes every other row)
+//       cv::pyrUp rows of the coarse flow kept in registers while marching, float32 map,
+//       32 gathers per lane issued back to back, blend -> warped A', B' row -> AB ring.
+//   consumer  (warp 2; lane = 4 consecutive columns)
+//       2x2 gradient stencils (previous row in registers), five products, horizontal window
+//       sums in registers + shuffles (additions only), vertical window sums by a van Herk /
+//       Gil-Werman block scheme over a (2R)-row shared-memory ring private to each lane,
+//       guarded solve with one shared reciprocal -> LK flow row -> LK ring.
+//   epilogue  (warp 3; lane = 4 consecutive columns)
+//       upsampled coarse flow at the output row, += (:634-637), 16-byte coalesced stores of
+//       u, v, optional mask and gesture statistics (:845-873).
+//
+// Shared-memory rows are "pair-split": a lane's columns (0,1) live at lo[2*lane], its columns
+// (2,3) at hi[2*lane], so every 128-bit access of a warp is contiguous and conflict-free.
+//
+// Window sums never subtract: an all-zero window sums to exactly 0, so det == 0 pixels keep
+// the reference's "zero divisor -> 0" behaviour (cv::divide, :514,518) bit for bit.  The
+// association order of the (2R+1)^2 terms differs from the oracle's row-major order by design
+// (no reference order exists for R > 1); tests bound the effect at 1e-3 px.
+//
+// HBM traffic per level-l pixel: read A, B (gathered, L2-friendly), read 1/4 coarse u, v,
+// write u, v  = 36 B algorithmic; everything else stays on chip.
+#include "of_device.cuh"
+#include "of_kernels.h"
+
+namespace ofb {
+
+namespace {
+
+constexpr int NB = 4;          // AB ring depth (rows); even: a slot always belongs to one producer
+constexpr int NE = 2;          // LK ring depth (rows)
+constexpr int AB_SLOT = 256;   // doubles per AB slot: A_lo[64] A_hi[64] B_lo[64] B_hi[64]
+
+template <int R>
+struct StripCfg {
+    static constexpr int Q = R / 4, RHO = R % 4;
+    static constexpr int HL = Q + 1;                  // halo lanes on each side
+    static constexpr int OUT_LANES = 32 - 2 * HL;
+    static constexpr int OUT_COLS = 4 * OUT_LANES;
+    static constexpr int HALF = OUT_COLS / 2;         // offset of the hi pairs inside a pair-split row
+    static constexpr int WIN = 2 * R + 1;             // vertical block length
+    static constexpr int VSLOTS = 2 * R;              // block rows 1 .. 2R are stored
+    static constexpr int VROW = 5 * OUT_COLS;         // doubles per ring slot (5 channels)
+    static constexpr size_t V_DOUBLES = (size_t)VSLOTS * VROW;
+    static constexpr size_t AB_DOUBLES = (size_t)NB * AB_SLOT;
+    static constexpr size_t LK_DOUBLES = (size_t)NE * 2 * OUT_COLS;
+    static constexpr size_t SMEM_BYTES = (V_DOUBLES + AB_DOUBLES + LK_DOUBLES) * 8 + (size_t)NE * 32 * 4;
+};
+
+// named barriers (id 0 is __syncthreads)
+constexpr int BAR_AB_FULL = 1;               // .. +NB-1
+constexpr int BAR_AB_EMPTY = 1 + NB;         // .. +NB-1
+constexpr int BAR_LK_FULL = 1 + 2 * NB;      // .. +NE-1
+constexpr int BAR_LK_EMPTY = 1 + 2 * NB + NE;
+
+__device__ __forceinline__ void bar_sync(int id, int n)
+{
+    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory");
+}
+__device__ __forceinline__ void bar_arrive(int id, int n)
+{
+    asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(n) : "memory");
+}
+
+struct Geo {          // per-CTA geometry, identical in all roles
+    int W, H;
+    int c0;           // image column of (lane 0, i 0); multiple of 4 (may be negative)
+    int xo0;          // first output column of the strip
+    int y0, y1;       // output rows [y0, y1)
+    int vy_first;     // first real product row = max(y0 - R, 0)
+    int vy_last;      // last real product row  = min(y1 - 1 + R, H - 1)
+    int n_deliv;      // rows the producers deliver = 1 (the row above vy_first) + real rows
+    bool has_coarse;
+    bool edge;        // strip touches the left or right image border (pyrUp border formulas)
+};
+
+__device__ __forceinline__ double2 lds2(const double* p) { return *reinterpret_cast<const double2*>(p); }
+__device__ __forceinline__ void sts2(double* p, double x, double y) { *reinterpret_cast<double2*>(p) = make_double2(x, y); }
+
+// pair-split 4-vector: p points at the lane's lo pair, the hi pair is `half` doubles further
+__device__ __forceinline__ void ld4s(const double* p, int half, double (&v)[4])
+{
+    const double2 a = lds2(p), b = lds2(p + half);
+    v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y;
+}
+__device__ __forceinline__ void st4s(double* p, int half, const double (&v)[4])
+{
+    sts2(p, v[0], v[1]);
+    sts2(p + half, v[2], v[3]);
+}
+
+// ---------------------------------------------------------------- cv::pyrUp while marching
+// Horizontal pass of cv::pyrUp (:646-647) for the lane's four fine columns xb .. xb+3 from one
+// coarse row: e0 o0 e1 o1.  j0 = xb / 2 (even), n = coarse width >= 2.  Warp-collective.
+struct H4 { double v[4]; };
+
+__device__ __forceinline__ H4 pyrup_hrow4(const double* __restrict__ row, int j0, int n, bool col_ok,
+                                          int xb, bool edge)
+{
+    const int lane = threadIdx.x & 31;
+    double s0 = 0.0, s1 = 0.0;
+    if (col_ok) {
+        if (j0 + 1 < n) {
+            const double2 t = __ldg(reinterpret_cast<const double2*>(row + j0));
+            s0 = t.x;
+            s1 = t.y;
+        } else {
+            s0 = __ldg(row + j0);
+        }
+    }
+    double sl = __shfl_up_sync(0xffffffffu, s1, 1);
+    double sr = __shfl_down_sync(0xffffffffu, s0, 1);
+    if (lane == 0 && col_ok && j0 > 0) sl = __ldg(row + j0 - 1);
+    if (lane == 31 && col_ok && j0 + 2 < n) sr = __ldg(row + j0 + 2);
+    H4 h;
+    h.v[0] = dadd(dadd(sl, dmul(s0, 6.0)), s1);
+    h.v[1] = dmul(dadd(s0, s1), 4.0);
+    h.v[2] = dadd(dadd(s0, dmul(s1, 6.0)), sr);
+    h.v[3] = dmul(dadd(s1, sr), 4.0);
+    if (edge) {                                   // warp-uniform: only strips touching a border
+        if (xb == 0) h.v[0] = dadd(dmul(s0, 6.0), dmul(s1, 2.0));
+        if (j0 + 1 == n - 1) { h.v[2] = dadd(s0, dmul(s1, 7.0)); h.v[3] = dmul(s1, 8.0); }
+        if (j0 == n - 1) { h.v[0] = dadd(sl, dmul(s0, 7.0)); h.v[1] = dmul(s0, 8.0); }
+    }
+    return h;
+}
+
+struct UpRows {       // pyrUp rows rho(k-1), k, rho(k+1) for the lane's 4 columns, u and v
+    H4 u0, u1, u2, v0, v1, v2;
+};
+
+struct UpCtx {
+    const double* __restrict__ cu;
+    const double* __restrict__ cv;
+    size_t cp;
+    int wc, hc;
+    int j0, xb;
+    bool col_ok, edge;
+};
+
+__device__ __forceinline__ void up_advance(UpRows& r, const UpCtx& c, int k, int kprev)
+{
+    if (k == kprev + 1) {
+        r.u0 = r.u1; r.u1 = r.u2;
+        r.v0 = r.v1; r.v1 = r.v2;
+    } else {
+        const size_t o0 = (size_t)pyrup_rho(k - 1, c.hc) * c.cp, o1 = (size_t)k * c.cp;
+        r.u0 = pyrup_hrow4(c.cu + o0, c.j0, c.wc, c.col_ok, c.xb, c.edge);
+        r.v0 = pyrup_hrow4(c.cv + o0, c.j0, c.wc, c.col_ok, c.xb, c.edge);
+        r.u1 = pyrup_hrow4(c.cu + o1, c.j0, c.wc, c.col_ok, c.xb, c.edge);
+        r.v1 = pyrup_hrow4(c.cv + o1, c.j0, c.wc, c.col_ok, c.xb, c.edge);
+    }
+    const size_t o2 = (size_t)pyrup_rho(k + 1, c.hc) * c.cp;
+    r.u2 = pyrup_hrow4(c.cu + o2, c.j0, c.wc, c.col_ok, c.xb, c.edge);
+    r.v2 = pyrup_hrow4(c.cv + o2, c.j0, c.wc, c.col_ok, c.xb, c.edge);
+}
+
+// Vertical pass of cv::pyrUp.  ((a+b)*4)*(1/64) == (a+b)*(1/16): both scalings are exact.
+__device__ __forceinline__ void up_eval(const UpRows& r, int y, double (&upu)[4], double (&upv)[4])
+{
+    if (y & 1) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            upu[i] = dmul(dadd(r.u1.v[i], r.u2.v[i]), 0.0625);
+            upv[i] = dmul(dadd(r.v1.v[i], r.v2.v[i]), 0.0625);
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            upu[i] = dmul(dadd(dadd(r.u0.v[i], dmul(r.u1.v[i], 6.0)), r.u2.v[i]), 0.015625);
+            upv[i] = dmul(dadd(dadd(r.v0.v[i], dmul(r.v1.v[i], 6.0)), r.v2.v[i]), 0.015625);
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------ producers
+// OpenCV remap fixed-point coordinate, without the int16 saturation of q5(): with images of at
+// most 32767 pixels per side an unsaturated out-of-range coordinate stays out of range.  NaN
+// maps far outside (fmaxf returns the non-NaN operand), like cvRound's INT_MIN.
+__device__ __forceinline__ int q5s(float m)
+{
+    const float t = fminf(fmaxf(__fmul_rn(m, 32.0f), -1073741824.0f), 1073741824.0f);
+    return __float2int_rn(t);
+}
+
+struct Tap {
+    int off;          // element offset of tap (iy, ix), clamped to (0,0) when not interior
+    int ax, ay;       // 5-bit fractions
+    bool interior;    // all four taps inside the image
+};
+
+__device__ __forceinline__ Tap make_tap(float mx, float my, int w, int h, int pitch)
+{
+    const int sx = q5s(mx), sy = q5s(my);
+    const int ix = sx >> 5, iy = sy >> 5;
+    Tap t;
+    t.ax = sx & 31;
+    t.ay = sy & 31;
+    t.interior = (unsigned)ix < (unsigned)(w - 1) && (unsigned)iy < (unsigned)(h - 1);
+    t.off = t.interior ? iy * pitch + ix : 0;
+    return t;
+}
+
+__device__ __forceinline__ double blend4(double s00, double s01, double s10, double s11, int ax, int ay)
+{
+    const double w00 = q10_to_double((32 - ay) * (32 - ax));
+    const double w01 = q10_to_double((32 - ay) * ax);
+    const double w10 = q10_to_double(ay * (32 - ax));
+    const double w11 = q10_to_double(ay * ax);
+    return dadd(dadd(dadd(dmul(s00, w00), dmul(s01, w01)), dmul(s10, w10)), dmul(s11, w11));
+}
+
+template <int R>
+__device__ __forceinline__ void producer_role(const LevelArgs& a, const Geo& g, int pair, double* s_ab, int par)
+{
+    const int lane = threadIdx.x & 31;
+    const int xb = g.c0 + 4 * lane;
+    const bool col_ok = xb >= 0 && xb < g.W;          // W is even and xb % 4 == 0: xb, xb+1 valid
+    const bool full4 = xb + 3 < g.W;                  // else W % 4 == 2 and only two columns exist
+    const int W = g.W, H = g.H;
+    const int pitch = (int)a.img_pitch;
+    const double* __restrict__ A = a.A + (size_t)pair * a.a_pair_stride;
+    const double* __restrict__ B = a.B + (size_t)pair * a.b_pair_stride;
+    const bool vec_in = ((reinterpret_cast<uintptr_t>(A) | reinterpret_cast<uintptr_t>(B) |
+                          (a.img_pitch * 8)) & 15) == 0;
+    UpCtx uc;
+    uc.cu = g.has_coarse ? a.cu + (size_t)pair * a.c_pair_stride : nullptr;
+    uc.cv = g.has_coarse ? a.cv + (size_t)pair * a.c_pair_stride : nullptr;
+    uc.cp = a.c_pitch;
+    uc.wc = a.wc;
+    uc.hc = a.hc;
+    uc.j0 = xb >> 1;
+    uc.xb = xb;
+    uc.col_ok = col_ok;
+    uc.edge = g.edge;
+    UpRows up;
+    int kprev = -100;
+    const float xf = (float)xb;
+
+    for (int d = par; d < g.n_deliv; d += 2) {
+        const int yy = (d == 0) ? r101(g.vy_first - 1, H) : g.vy_first + d - 1;
+        const int slot = d & (NB - 1);
+        double va[4], vb[4];
+        if (g.has_coarse) {
+            const int k = yy >> 1;
+            if (k != kprev) up_advance(up, uc, k, kprev);
+            kprev = k;
+            double upu[4], upv[4];
+            up_eval(up, yy, upu, upv);
+            const float yf = (float)yy;
+            Tap ta[4], tb[4];
+            bool all_in = true;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                float m1x, m1y, m2x, m2y;
+                const float fu = __double2float_rn(upu[i]), fv = __double2float_rn(upv[i]);
+                const float hu = __fmul_rn(fu, 0.5f), hv = __fmul_rn(fv, 0.5f);   // == f / 2 exactly
+                const float xfi = xf + (float)i;
+                m1x = __fadd_rn(xfi, hu);
+                m1y = __fadd_rn(yf, hv);
+                m2x = __fsub_rn(xfi, hu);
+                m2y = __fsub_rn(yf, hv);
+                ta[i] = make_tap(m1x, m1y, W, H, pitch);
+                tb[i] = make_tap(m2x, m2y, W, H, pitch);
+                all_in = all_in && ta[i].interior && tb[i].interior;
+            }
+            // 32 independent gathers per lane, issued before the first use
+            double sa[4][4], sb[4][4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const double* pa = A + ta[i].off;
+                const double* pb = B + tb[i].off;
+                sa[i][0] = __ldg(pa); sa[i][1] = __ldg(pa + 1);
+                sa[i][2] = __ldg(pa + pitch); sa[i][3] = __ldg(pa + pitch + 1);
+                sb[i][0] = __ldg(pb); sb[i][1] = __ldg(pb + 1);
+                sb[i][2] = __ldg(pb + pitch); sb[i][3] = __ldg(pb + pitch + 1);
+            }
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                va[i] = blend4(sa[i][0], sa[i][1], sa[i][2], sa[i][3], ta[i].ax, ta[i].ay);
+                vb[i] = blend4(sb[i][0], sb[i][1], sb[i][2], sb[i][3], tb[i].ax, tb[i].ay);
+            }
+            if (!all_in && col_ok) {
+                // rare: a tap outside the image -> BORDER_CONSTANT 0 tested per tap
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    if (!(ta[i].interior && tb[i].interior)) {
+                        float m1x, m1y, m2x, m2y;
+                        map_coords(xb + i, yy, upu[i], upv[i], m1x, m1y, m2x, m2y);
+                        if (!ta[i].interior) va[i] = remap_tap4(A, a.img_pitch, W, H, m1x, m1y);
+                        if (!tb[i].interior) vb[i] = remap_tap4(B, a.img_pitch, W, H, m2x, m2y);
+                    }
+                }
+            }
+            if (!col_ok) {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) va[i] = vb[i] = 0.0;
+            } else if (!full4) {
+                va[2] = va[3] = vb[2] = vb[3] = 0.0;
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) va[i] = vb[i] = 0.0;
+            if (col_ok) {
+                const double* pa = A + (size_t)yy * a.img_pitch + xb;
+                const double* pb = B + (size_t)yy * a.img_pitch + xb;
+                if (vec_in && full4) {
+                    const double2 a0 = __ldg(reinterpret_cast<const double2*>(pa));
+                    const double2 a1 = __ldg(reinterpret_cast<const double2*>(pa + 2));
+                    const double2 b0 = __ldg(reinterpret_cast<const double2*>(pb));
+                    const double2 b1 = __ldg(reinterpret_cast<const double2*>(pb + 2));
+                    va[0] = a0.x; va[1] = a0.y; va[2] = a1.x; va[3] = a1.y;
+                    vb[0] = b0.x; vb[1] = b0.y; vb[2] = b1.x; vb[3] = b1.y;
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 4; ++i)
+                        if (xb + i < W) { va[i] = __ldg(pa + i); vb[i] = __ldg(pb + i); }
+                }
+            }
+        }
+        if (d >= NB) bar_sync(BAR_AB_EMPTY + slot, 64);
+        double* ra = s_ab + slot * AB_SLOT + 2 * lane;
+        st4s(ra, 64, va);
+        st4s(ra + 128, 64, vb);
+        bar_arrive(BAR_AB_FULL + slot, 64);
+    }
+}
+
+// ------------------------------------------------------------------------------ consumer
+template <int OFF>
+__device__ __forceinline__ double lane_fetch(double v)
+{
+    if constexpr (OFF == 0) return v;
+    else if constexpr (OFF < 0) return __shfl_up_sync(0xffffffffu, v, -OFF);
+    else return __shfl_down_sync(0xffffffffu, v, OFF);
+}
+
+// Where the window [c-R, c+R] of output column c = 4j + I starts and ends in terms of the
+// 4-column groups owned by the lanes: partial suffix of group j+JL (LENL columns, 0 = none),
+// full groups j+FA .. j+FB, partial prefix of group j+JR (LENR columns, 0 = none).
+template <int R, int I>
+struct HWin {
+    static constexpr int Q = R / 4, RHO = R % 4;
+    static constexpr int D = I - RHO, E = I + RHO;
+    static constexpr int JL = D >= 0 ? -Q : -(Q + 1);
+    static constexpr int LENL = D > 0 ? 4 - D : (D == 0 ? 0 : -D);
+    static constexpr int FA = D > 0 ? -Q + 1 : -Q;
+    static constexpr int JR = E <= 3 ? Q : Q + 1;
+    static constexpr int LENR = E < 3 ? E + 1 : (E == 3 ? 0 : E - 3);
+    static constexpr int FB = E < 3 ? Q - 1 : Q;
+};
+
+// Groups j-QM .. j+QM are complete inside the window of all four columns of group j; their sum
+// M is formed once per lane (R >= 3).
+template <int R>
+struct HShare {
+    static constexpr bool USE = R >= 3;
+    static constexpr int QM = R >= 3 ? (R - 3) / 4 : -1;
+};
+
+template <int R, int I>
+__device__ __forceinline__ double hsum_one(const double (&pre)[4], const double (&suf)[4],
+                                           const double (&tj)[2 * (R / 4) + 1], double M)
+{
+    using Wn = HWin<R, I>;
+    using Sh = HShare<R>;
+    constexpr int Q = R / 4;
+    double acc = 0.0;
+    bool have = false;
+    if constexpr (Wn::LENL > 0) {
+        acc = lane_fetch<Wn::JL>(suf[Wn::LENL]);
+        have = true;
+    }
+#pragma unroll
+    for (int j = -Q; j <= Q; ++j) {
+        const bool in_m = Sh::USE && j >= -Sh::QM && j <= Sh::QM;
+        if (j >= Wn::FA && j <= Wn::FB && !in_m) {
+            acc = have ? dadd(acc, tj[j + Q]) : tj[j + Q];
+            have = true;
+        }
+    }
+    if constexpr (Sh::USE) {
+        acc = have ? dadd(acc, M) : M;
+        have = true;
+    }
+    if constexpr (Wn::LENR > 0) {
+        const double pr = lane_fetch<Wn::JR>(pre[Wn::LENR]);
+        acc = have ? dadd(acc, pr) : pr;
+    }
+    return acc;
+}
+
+// Horizontal (2R+1)-column window sums for the lane's four columns: group prefixes and
+// suffixes in registers, neighbours' pieces through shuffles; additions only.
+template <int R>
+__device__ __forceinline__ void hsum4(const double (&x)[4], double (&out)[4])
+{
+    constexpr int Q = R / 4;
+    using Sh = HShare<R>;
+    double pre[4], suf[4], tj[2 * Q + 1];
+    pre[1] = x[0];
+    pre[2] = dadd(x[0], x[1]);
+    pre[3] = dadd(pre[2], x[2]);
+    const double T = dadd(pre[3], x[3]);
+    suf[1] = x[3];
+    suf[2] = dadd(x[2], x[3]);
+    suf[3] = dadd(x[1], suf[2]);
+    pre[0] = suf[0] = 0.0;
+    tj[Q] = T;
+    if constexpr (Q >= 1) { tj[Q - 1] = lane_fetch<-1>(T); tj[Q + 1] = lane_fetch<1>(T); }
+    if constexpr (Q >= 2) { tj[Q - 2] = lane_fetch<-2>(T); tj[Q + 2] = lane_fetch<2>(T); }
+    if constexpr (Q >= 3) { tj[Q - 3] = lane_fetch<-3>(T); tj[Q + 3] = lane_fetch<3>(T); }
+    double M = 0.0;
+    if constexpr (Sh::USE) {
+        M = tj[Q - Sh::QM];
+#pragma unroll
+        for (int j = -Sh::QM + 1; j <= Sh::QM; ++j) M = dadd(M, tj[j + Q]);
+    }
+    out[0] = hsum_one<R, 0>(pre, suf, tj, M);
+    out[1] = hsum_one<R, 1>(pre, suf, tj, M);
+    out[2] = hsum_one<R, 2>(pre, suf, tj, M);
+    out[3] = hsum_one<R, 3>(pre, suf, tj, M);
+}
+
+// u = nu / det, v = nv / det, both correctly rounded (== __ddiv_rn bit for bit), sharing the
+// reciprocal refinement.  This is the fast path of CUDA's own IEEE division (MUFU.RCP64H seed,
+// two Newton steps, quotient, residual correction), taken under the same exponent-range
+// conditions; returns false when they do not hold (the caller then uses the library division).
+__device__ __noinline__ double ddiv_slow(double a, double b) { return __ddiv_rn(a, b); }
+
+__device__ __forceinline__ bool div2_fast(double nu, double nv, double det, double& u, double& v)
+{
+    double y;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(det));
+    y = __hiloint2double(__double2hiint(y), 1);
+    double e = __fma_rn(-det, y, 1.0);
+    e = __fma_rn(e, e, e);
+    y = __fma_rn(y, e, y);
+    e = __fma_rn(-det, y, 1.0);
+    y = __fma_rn(y, e, y);
+    double qu = dmul(nu, y);
+    double qv = dmul(nv, y);
+    qu = __fma_rn(y, __fma_rn(-det, qu, nu), qu);
+    qv = __fma_rn(y, __fma_rn(-det, qv, nv), qv);
+    const float tiny_q = __int_as_float(0x00100000), tiny_n = __int_as_float(0x03600000);
+    const float dh = __int_as_float(__double2hiint(det));
+    // a zero numerator gives a zero quotient on the fast path too (the sign of that zero is
+    // not observable downstream), so it does not need the library path
+    const bool ok_u = (fabsf(__fmaf_rn(0.0f, dh, __int_as_float(__double2hiint(qu)))) > tiny_q &&
+                       fabsf(__int_as_float(__double2hiint(nu))) >= tiny_n) || nu == 0.0;
+    const bool ok_v = (fabsf(__fmaf_rn(0.0f, dh, __int_as_float(__double2hiint(qv)))) > tiny_q &&
+                       fabsf(__int_as_float(__double2hiint(nv))) >= tiny_n) || nv == 0.0;
+    u = qu;
+    v = qv;
+    return ok_u && ok_v;
+}
+
+template <int R>
+__device__ __forceinline__ void consumer_role(const LevelArgs& a, const Geo& g, const double* s_ab,
+                                              double* s_v, double* s_lk, unsigned* s_mk)
+{
+    using C = StripCfg<R>;
+    const int lane = threadIdx.x & 31;
+    const bool active = lane >= C::HL && lane < 32 - C::HL;
+    const int xb = g.c0 + 4 * lane;                 // image column of i = 0
+    const int ol = active ? lane - C::HL : 0;       // output lane
+    const int W = g.W, H = g.H;
+    const double* ab_lane = s_ab + 2 * lane;
+    double* v_lane = s_v + 2 * ol;
+    double* lk_lane = s_lk + 2 * ol;
+    const double det_eps = a.det_eps;
+
+    double prevA[4], prevB[4], prevLA, prevLB;
+    double P[5][4];
+#pragma unroll
+    for (int c = 0; c < 5; ++c)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) P[c][i] = 0.0;
+
+    int dd = 0;   // deliveries consumed so far
+    {   // the row above the first product row (reflect-101 at the image top)
+        bar_sync(BAR_AB_FULL + 0, 64);
+        ld4s(ab_lane, 64, prevA);
+        ld4s(ab_lane + 128, 64, prevB);
+        prevLA = ab_lane[64 - 1];
+        prevLB = ab_lane[192 - 1];
+        if (dd + NB < g.n_deliv) bar_arrive(BAR_AB_EMPTY + 0, 64);
+        dd = 1;
+    }
+
+    const int th = g.y1 - g.y0;
+    const int n_virtual = th + 2 * R;
+    int ib = 0;
+    double* vp = v_lane;                             // ring slot ib
+    for (int n = 0; n < n_virtual; ++n) {
+        const int vy = g.y0 - R + n;
+        double fx[4], fy[4], ft[4];
+        if (vy >= 0 && vy < H) {
+            const int slot = dd & (NB - 1);
+            bar_sync(BAR_AB_FULL + slot, 64);
+            const double* ra = ab_lane + slot * AB_SLOT;
+            double curA[4], curB[4];
+            ld4s(ra, 64, curA);
+            ld4s(ra + 128, 64, curB);
+            double curLA = ra[64 - 1];
+            double curLB = ra[192 - 1];
+            if (dd + NB < g.n_deliv) bar_arrive(BAR_AB_EMPTY + slot, 64);
+            ++dd;
+            if (xb == 0) {                           // reflect-101 at the left image border
+                const bool w1 = W > 1;
+                curLA = w1 ? curA[1] : curA[0];
+                curLB = w1 ? curB[1] : curB[0];
+                prevLA = w1 ? prevA[1] : prevA[0];
+                prevLB = w1 ? prevB[1] : prevB[0];
+            }
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const double a00 = i ? prevA[i - 1] : prevLA, a01 = prevA[i];
+                const double a10 = i ? curA[i - 1] : curLA, a11 = curA[i];
+                const double b00 = i ? prevB[i - 1] : prevLB, b01 = prevB[i];
+                const double b10 = i ? curB[i - 1] : curLB, b11 = curB[i];
+                // filter2D accumulation order ((k00 p00 + k01 p01) + k10 p10) + k11 p11 (:44-84)
+                const double fxa = dadd(dsub(dsub(a01, a00), a10), a11);
+                const double fxb = dadd(dsub(dsub(b01, b00), b10), b11);
+                const double sa = dadd(a00, a01), sb = dadd(b00, b01);
+                const double fya = dadd(dsub(a10, sa), a11);
+                const double fyb = dadd(dsub(b10, sb), b11);
+                const double fta = -dadd(dadd(sa, a10), a11);
+                const double ftb = dadd(dadd(sb, b10), b11);
+                const bool in = (unsigned)(xb + i) < (unsigned)W;
+                fx[i] = in ? dadd(fxa, fxb) : 0.0;
+                fy[i] = in ? dadd(fya, fyb) : 0.0;
+                ft[i] = in ? dadd(fta, ftb) : 0.0;
+            }
+#pragma unroll
+            for (int i = 0; i < 4; ++i) { prevA[i] = curA[i]; prevB[i] = curB[i]; }
+            prevLA = curLA;
+            prevLB = curLB;
+        } else {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) fx[i] = fy[i] = ft[i] = 0.0;
+        }
+
+        const bool emit = n >= C::WIN - 1;
+        const bool last = ib == C::WIN - 1;
+        double S[5][4];
+#pragma unroll
+        for (int c = 0; c < 5; ++c) {
+            double x[4], h[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                // fx2, fy2, fxfy, fxft, fyft (:383-405)
+                const double p = (c == 1 || c == 4) ? fy[i] : fx[i];
+                const double q = c == 0 ? fx[i] : (c <= 2 ? fy[i] : ft[i]);
+                x[i] = dmul(p, q);
+            }
+            hsum4<R>(x, h);
+            if (active) {
+                // vertical van Herk / Gil-Werman: P = running prefix of the current block,
+                // the ring holds the suffix sums of the previous block, overwritten row by row.
+                double* vrow = vp + c * C::OUT_COLS;             // slot ib  <-> block row ib+1
+                if (ib == 0) {
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) P[c][i] = h[i];
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) P[c][i] = dadd(P[c][i], h[i]);
+                }
+                if (emit && !last) {
+                    double sp[4];
+                    ld4s(vrow, C::HALF, sp);                     // suffix of previous block from row ib+1
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) S[c][i] = dadd(sp[i], P[c][i]);
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) S[c][i] = P[c][i];
+                }
+                if (ib >= 1) st4s(vrow - C::VROW, C::HALF, h);   // raw row ib -> slot ib-1
+            }
+        }
+
+        if (last && active) {
+            // block finished: turn the stored raw rows 1..2R into suffix sums, in place
+#pragma unroll
+            for (int c = 0; c < 5; ++c) {
+                double acc[4];
+                double* vr = v_lane + (C::VSLOTS - 1) * C::VROW + c * C::OUT_COLS;
+                ld4s(vr, C::HALF, acc);
+#pragma unroll 2
+                for (int t = C::VSLOTS - 2; t >= 0; --t) {
+                    vr -= C::VROW;
+                    double raw[4];
+                    ld4s(vr, C::HALF, raw);
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) acc[i] = dadd(raw[i], acc[i]);
+                    st4s(vr, C::HALF, acc);
+                }
+            }
+        }
+
+        if (emit) {
+            const int m = n - (C::WIN - 1);
+            const int y = g.y0 + m;
+            const int eslot = m & (NE - 1);
+            if (m >= NE) bar_sync(BAR_LK_EMPTY + eslot, 64);
+            if (active) {
+                const bool yin = y >= R && y <= H - 1 - R;
+                double lu[4], lv[4], nus[4], nvs[4], dets[4];
+                unsigned okbits = 0;
+                bool fast = true;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const int x = xb + i;
+                    const bool interior = yin && x >= R && x <= W - 1 - R;
+                    const double sxx = S[0][i], syy = S[1][i], sxy = S[2][i], sxt = S[3][i], syt = S[4][i];
+                    const double det = dsub(dmul(sxx, syy), dmul(sxy, sxy));
+                    const double nu = dsub(dmul(sxy, syt), dmul(syy, sxt));
+                    const double nv = dsub(dmul(sxt, sxy), dmul(sxx, syt));
+                    const bool ok = interior && fabs(det) > det_eps;
+                    dets[i] = ok ? det : 1.0;
+                    nus[i] = ok ? nu : 1.0;
+                    nvs[i] = ok ? nv : 1.0;
+                    okbits |= ok ? (1u << (8 * i)) : 0u;
+                    fast = div2_fast(nus[i], nvs[i], dets[i], lu[i], lv[i]) && fast;
+                }
+                if (!fast) {                         // rare: exponent range outside the fast path
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        lu[i] = ddiv_slow(nus[i], dets[i]);
+                        lv[i] = ddiv_slow(nvs[i], dets[i]);
+                    }
+                }
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const bool ok = (okbits >> (8 * i)) & 1u;
+                    lu[i] = ok ? lu[i] : 0.0;
+                    lv[i] = ok ? lv[i] : 0.0;
+                }
+                double* lk = lk_lane + eslot * 2 * C::OUT_COLS;
+                st4s(lk, C::HALF, lu);
+                st4s(lk + C::OUT_COLS, C::HALF, lv);
+                s_mk[eslot * 32 + lane] = okbits;
+            }
+            bar_arrive(BAR_LK_FULL + eslot, 64);
+        }
+        if (last) { ib = 0; vp = v_lane; } else { ++ib; vp += C::VROW; }
+    }
+}
+
+// ------------------------------------------------------------------------------ epilogue
+template <int R>
+__device__ __forceinline__ void epilogue_role(const LevelArgs& a, const Geo& g, int pair,
+                                              const double* s_lk, const unsigned* s_mk)
+{
+    using C = StripCfg<R>;
+    const int lane = threadIdx.x & 31;
+    const bool active = lane >= C::HL && lane < 32 - C::HL;
+    const int xb = g.c0 + 4 * lane;
+    const int ol = active ? lane - C::HL : 0;
+    const int W = g.W;
+    const bool col_ok = xb >= 0 && xb < W;
+    const bool store = active && col_ok;
+    const bool full4 = xb + 3 < W;
+    UpCtx uc;
+    uc.cu = g.has_coarse ? a.cu + (size_t)pair * a.c_pair_stride : nullptr;
+    uc.cv = g.has_coarse ? a.cv + (size_t)pair * a.c_pair_stride : nullptr;
+    uc.cp = a.c_pitch;
+    uc.wc = a.wc;
+    uc.hc = a.hc;
+    uc.j0 = xb >> 1;
+    uc.xb = xb;
+    uc.col_ok = col_ok;
+    uc.edge = g.edge;
+    double* __restrict__ U = a.u ? a.u + (size_t)pair * a.uv_pair_stride : nullptr;
+    double* __restrict__ V = a.v ? a.v + (size_t)pair * a.uv_pair_stride : nullptr;
+    unsigned char* __restrict__ M = a.mask ? a.mask + (size_t)pair * a.mask_pair_stride : nullptr;
+    const bool vec_out = U && ((reinterpret_cast<uintptr_t>(U) | reinterpret_cast<uintptr_t>(V) |
+                                (a.uv_pitch * 8)) & 15) == 0;
+    const double* lk_lane = s_lk + 2 * ol;
+    const double mag2 = a.mag2_thresh;
+    UpRows up;
+    int kprev = -100;
+    unsigned long long st_x = 0, st_y = 0, st_c = 0;   // exact integer partial sums of this lane
+    const int th = g.y1 - g.y0;
+    for (int m = 0; m < th; ++m) {
+        const int y = g.y0 + m;
+        const int eslot = m & (NE - 1);
+        double upu[4], upv[4];
+        if (g.has_coarse) {                          // upsampled coarse flow first (global loads)
+            const int k = y >> 1;
+            if (k != kprev) up_advance(up, uc, k, kprev);
+            kprev = k;
+            up_eval(up, y, upu, upv);
+        }
+        bar_sync(BAR_LK_FULL + eslot, 64);
+        double fu[4], fv[4];
+        const double* lk = lk_lane + eslot * 2 * C::OUT_COLS;
+        ld4s(lk, C::HALF, fu);
+        ld4s(lk + C::OUT_COLS, C::HALF, fv);
+        const unsigned okbits = s_mk[eslot * 32 + lane];
+        if (m + NE < th) bar_arrive(BAR_LK_EMPTY + eslot, 64);
+        if (g.has_coarse) {                          // tmpu += upu; tmpv += upv  (:634-637)
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                fu[i] = dadd(fu[i], upu[i]);
+                fv[i] = dadd(fv[i], upv[i]);
+            }
+        }
+        if (store) {
+            if (U) {
+                double* pu = U + (size_t)y * a.uv_pitch + xb;
+                double* pv = V + (size_t)y * a.uv_pitch + xb;
+                if (vec_out && full4) {
+                    *reinterpret_cast<double2*>(pu) = make_double2(fu[0], fu[1]);
+                    *reinterpret_cast<double2*>(pu + 2) = make_double2(fu[2], fu[3]);
+                    *reinterpret_cast<double2*>(pv) = make_double2(fv[0], fv[1]);
+                    *reinterpret_cast<double2*>(pv + 2) = make_double2(fv[2], fv[3]);
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 4; ++i)
+                        if (xb + i < W) { pu[i] = fu[i]; pv[i] = fv[i]; }
+                }
+            }
+            if (M) {
+                unsigned char* pm = M + (size_t)y * a.mask_pitch + xb;
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+                    if (xb + i < W) pm[i] = (unsigned char)((okbits >> (8 * i)) & 1u);
+            }
+            if (a.stats) {
+                unsigned rc = 0;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    // val = sqrt(u^2 + v^2); !(val < mag_thresh)  <=>  !(u^2 + v^2 < mag2)   (:850-873)
+                    const double s2 = dadd(dmul(fu[i], fu[i]), dmul(fv[i], fv[i]));
+                    if (xb + i < W && !(s2 < mag2)) { st_x += (unsigned)(xb + i); rc += 1u; }
+                }
+                st_c += rc;
+                st_y += (unsigned long long)rc * (unsigned)y;
+            }
+        }
+    }
+    if (a.stats) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            st_x += __shfl_xor_sync(0xffffffffu, st_x, o);
+            st_y += __shfl_xor_sync(0xffffffffu, st_y, o);
+            st_c += __shfl_xor_sync(0xffffffffu, st_c, o);
+        }
+        if (lane == 0 && st_c != 0) {                // integer-valued sums: exact in any order
+            atomicAdd(&a.stats[pair].sum_x, (double)st_x);
+            atomicAdd(&a.stats[pair].sum_y, (double)st_y);
+            atomicAdd(&a.stats[pair].count, (double)st_c);
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------ kernel
+template <int R>
+__global__ void __launch_bounds__(128, 3) lk_level_strip_kernel(LevelArgs a, int th)
+{
+    using C = StripCfg<R>;
+    extern __shared__ __align__(16) double sm[];
+    double* s_v = sm;
+    double* s_ab = s_v + C::V_DOUBLES;
+    double* s_lk = s_ab + C::AB_DOUBLES;
+    unsigned* s_mk = reinterpret_cast<unsigned*>(s_lk + C::LK_DOUBLES);
+
+    Geo g;
+    g.W = a.w;
+    g.H = a.h;
+    g.xo0 = blockIdx.x * C::OUT_COLS;
+    g.c0 = g.xo0 - 4 * C::HL;
+    g.y0 = blockIdx.y * th;
+    g.y1 = min(g.y0 + th, a.h);
+    g.vy_first = max(g.y0 - R, 0);
+    g.vy_last = min(g.y1 - 1 + R, a.h - 1);
+    g.n_deliv = g.vy_last - g.vy_first + 2;
+    g.has_coarse = a.cu != nullptr;
+    g.edge = g.xo0 == 0 || g.c0 + 132 >= a.w;
+    const int pair = blockIdx.z;
+
+    const int role = threadIdx.x >> 5;
+    if (role <= 1) producer_role<R>(a, g, pair, s_ab, role);
+    else if (role == 2) consumer_role<R>(a, g, s_ab, s_v, s_lk, s_mk);
+    else epilogue_role<R>(a, g, pair, s_lk, s_mk);
+}
+
+template <int R>
+cudaError_t launch_strip(const LevelArgs& a, int n_pairs, cudaStream_t s, unsigned long long* launches)
+{
+    using C = StripCfg<R>;
+    static bool attr_done = false;
+    if (!attr_done) {
+        cudaError_t e = cudaFuncSetAttribute(lk_level_strip_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)C::SMEM_BYTES);
+        if (e != cudaSuccess) return e;
+        attr_done = true;
+    }
+    const int strips = (a.w + C::OUT_COLS - 1) / C::OUT_COLS;
+    // Chunk height: a multiple of the vertical block length (2R+1), so that the block
+    // boundaries of the vertical sums sit at the same absolute rows whatever the chunking --
+    // results are then bit-identical for any batch size.  Pick the height that minimises
+    // (waves of resident CTAs) x (rows a CTA marches, including its 2R warm-up rows).
+    const long resident = 148L * 3;
+    const int max_m = (a.h + C::WIN - 1) / C::WIN;
+    long best_cost = -1;
+    int th = C::WIN * max_m;
+    for (int m = 2; m <= max_m; ++m) {
+        const int t = C::WIN * m;
+        const long chunks = (a.h + t - 1) / t;
+        const long ctas = (long)strips * chunks * n_pairs;
+        const long waves = (ctas + resident - 1) / resident;
+        const long cost = waves * (t + 2 * R + 6);
+        if (best_cost < 0 || cost < best_cost) { best_cost = cost; th = t; }
+    }
+    if (th > a.h) th = a.h;
+    const int chunks = (a.h + th - 1) / th;
+    dim3 grid(strips, chunks, n_pairs);
+    lk_level_strip_kernel<R><<<grid, 128, C::SMEM_BYTES, s>>>(a, th);
+    if (launches) *launches += 1;
+    return cudaGetLastError();
+}
+
+}  // namespace
+
+// Handles R = 2..7 on levels that are at least one window tall and two coarse columns wide;
+// everything else (R = 1 bit-exact order, tiny levels) goes to the generic tile kernel.
+cudaError_t launch_lk_level_strip(const LevelArgs& a, int n_pairs, cudaStream_t s,
+                                  unsigned long long* launches, bool* handled)
+{
+    *handled = false;
+    if (a.w < 4 || a.h < 2 || (a.w & 1)) return cudaSuccess;
+    if (a.cu && (a.wc < 2 || a.w != 2 * a.wc || a.h != 2 * a.hc)) return cudaSuccess;
+    if ((unsigned long long)a.img_pitch * (unsigned long long)a.h >= (1ull << 31)) return cudaSuccess;
+    *handled = true;
+    switch (a.radius) {
+        case 2: return launch_strip<2>(a, n_pairs, s, launches);
+        case 3: return launch_strip<3>(a, n_pairs, s, launches);
+        case 4: return launch_strip<4>(a, n_pairs, s, launches);
+        case 5: return launch_strip<5>(a, n_pairs, s, launches);
+        case 6: return launch_strip<6>(a, n_pairs, s, launches);
+        case 7: return launch_strip<7>(a, n_pairs, s, launches);
+        default: break;
+    }
+    *handled = false;
+    return cudaSuccess;
+}
+
+}  // namespace ofb

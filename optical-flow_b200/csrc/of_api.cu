@@ -6,6 +6,7 @@
 // or returns an error code.
 #include <cuda_runtime.h>
 
+#include <cmath>
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
@@ -19,6 +20,8 @@ namespace ofb {
 cudaError_t launch_lk_level_tile(const LevelArgs& a, int n_pairs, cudaStream_t s,
                                  unsigned long long* launches);
 cudaError_t launch_lk_level_march(const LevelArgs& a, int n_pairs, cudaStream_t s,
+                                  unsigned long long* launches, bool* handled);
+cudaError_t launch_lk_level_strip(const LevelArgs& a, int n_pairs, cudaStream_t s,
                                   unsigned long long* launches, bool* handled);
 }  // namespace ofb
 
@@ -48,7 +51,7 @@ struct of_ctx {
     Arena staging;                     // device copies of host-pointer inputs/outputs
     std::string err;
     unsigned long long launches = 0;
-    int force_variant = 0;             // 0 auto, 1 tile, 2 march (test hook via OF_B200_VARIANT)
+    int force_variant = 0;             // 0 auto, 1 tile, 2 march, 3 strip (test hook via OF_B200_VARIANT)
     // optional per-launch device timing of the most recent batch call (bench roofline evidence)
     bool timing = false;
     std::vector<cudaEvent_t> tev;      // 2 events per timed launch
@@ -162,6 +165,23 @@ of_status check_common(of_ctx* ctx, const void* a, const void* b, int w, int h, 
     return OF_OK;
 }
 
+// Smallest double s with !(sqrt(s) < t), so that  !(sqrt(s2) < t)  <=>  !(s2 < s)  for every
+// s2 >= 0 (sqrt is correctly rounded and monotonic).  Gesture statistics, :850-873.
+double mag2_threshold(double t)
+{
+    if (!(t > 0.0)) return 0.0;                    // t <= 0 or NaN: nothing is below the threshold
+    if (std::isinf(t)) return t;
+    double s = t * t;
+    if (std::isinf(s)) return s;
+    while (std::sqrt(s) < t) s = std::nextafter(s, INFINITY);
+    for (;;) {
+        const double p = std::nextafter(s, 0.0);
+        if (p == s || std::sqrt(p) < t) break;
+        s = p;
+    }
+    return s;
+}
+
 // Brackets one kernel launch with events on the launching stream when timing is enabled.
 struct TimedLaunch {
     of_ctx* ctx;
@@ -193,11 +213,15 @@ struct TimedLaunch {
 
 cudaError_t launch_lk_level(of_ctx* ctx, const ofb::LevelArgs& a, int n_pairs, cudaStream_t s)
 {
-    if (ctx->force_variant != 1) {
+    if (ctx->force_variant == 0 || ctx->force_variant == 3) {
+        bool handled = false;
+        cudaError_t e = ofb::launch_lk_level_strip(a, n_pairs, s, &ctx->launches, &handled);
+        if (handled || e != cudaSuccess) return e;
+    }
+    if (ctx->force_variant == 2) {
         bool handled = false;
         cudaError_t e = ofb::launch_lk_level_march(a, n_pairs, s, &ctx->launches, &handled);
         if (handled || e != cudaSuccess) return e;
-        if (ctx->force_variant == 2) return cudaErrorNotSupported;
     }
     return ofb::launch_lk_level_tile(a, n_pairs, s, &ctx->launches);
 }
@@ -282,6 +306,7 @@ of_status run_batch(of_ctx* ctx, int n_pairs, const double* img1, const double* 
         a.radius = ctx->params.win_radius;
         a.det_eps = ctx->params.det_eps;
         a.mag_thresh = ctx->params.mag_thresh;
+        a.mag2_thresh = mag2_threshold(ctx->params.mag_thresh);
         if (l == 0) {
             a.A = img1;
             a.B = img2;
@@ -379,6 +404,7 @@ of_status of_ctx_create(int device, const of_params* params, of_ctx** out)
     if (const char* fv = getenv("OF_B200_VARIANT")) {
         if (!strcmp(fv, "tile")) ctx->force_variant = 1;
         else if (!strcmp(fv, "march")) ctx->force_variant = 2;
+        else if (!strcmp(fv, "strip")) ctx->force_variant = 3;
     }
     e = cudaSetDevice(device);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);

@@ -30,6 +30,7 @@ struct LevelArgs {
     size_t mask_pair_stride;
     of_gesture_stats* stats;  // may be nullptr; accumulated with atomics (pre-zeroed)
     double mag_thresh;
+    double mag2_thresh;       // smallest s with !(sqrt(s) < mag_thresh): lets kernels skip the sqrt
     int w, h;
     int radius;
     double det_eps;
