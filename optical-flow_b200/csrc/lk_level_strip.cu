@@ -83,6 +83,7 @@ struct Geo {          // per-CTA geometry, identical in all roles
     bool edge;        // strip touches the left or right image border (pyrUp border formulas)
 };
 
+__device__ __forceinline__ void prefetch_l1(const double* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
 __device__ __forceinline__ double2 lds2(const double* p) { return *reinterpret_cast<const double2*>(p); }
 __device__ __forceinline__ void sts2(double* p, double x, double y) { *reinterpret_cast<double2*>(p) = make_double2(x, y); }
 
@@ -102,41 +103,7 @@ __device__ __forceinline__ void st4s(double* p, int half, const double (&v)[4])
 // Horizontal pass of cv::pyrUp (:646-647) for the lane's four fine columns xb .. xb+3 from one
 // coarse row: e0 o0 e1 o1.  j0 = xb / 2 (even), n = coarse width >= 2.  Warp-collective.
 struct H4 { double v[4]; };
-
-__device__ __forceinline__ H4 pyrup_hrow4(const double* __restrict__ row, int j0, int n, bool col_ok,
-                                          int xb, bool edge)
-{
-    const int lane = threadIdx.x & 31;
-    double s0 = 0.0, s1 = 0.0;
-    if (col_ok) {
-        if (j0 + 1 < n) {
-            const double2 t = __ldg(reinterpret_cast<const double2*>(row + j0));
-            s0 = t.x;
-            s1 = t.y;
-        } else {
-            s0 = __ldg(row + j0);
-        }
-    }
-    double sl = __shfl_up_sync(0xffffffffu, s1, 1);
-    double sr = __shfl_down_sync(0xffffffffu, s0, 1);
-    if (lane == 0 && col_ok && j0 > 0) sl = __ldg(row + j0 - 1);
-    if (lane == 31 && col_ok && j0 + 2 < n) sr = __ldg(row + j0 + 2);
-    H4 h;
-    h.v[0] = dadd(dadd(sl, dmul(s0, 6.0)), s1);
-    h.v[1] = dmul(dadd(s0, s1), 4.0);
-    h.v[2] = dadd(dadd(s0, dmul(s1, 6.0)), sr);
-    h.v[3] = dmul(dadd(s1, sr), 4.0);
-    if (edge) {                                   // warp-uniform: only strips touching a border
-        if (xb == 0) h.v[0] = dadd(dmul(s0, 6.0), dmul(s1, 2.0));
-        if (j0 + 1 == n - 1) { h.v[2] = dadd(s0, dmul(s1, 7.0)); h.v[3] = dmul(s1, 8.0); }
-        if (j0 == n - 1) { h.v[0] = dadd(sl, dmul(s0, 7.0)); h.v[1] = dmul(s0, 8.0); }
-    }
-    return h;
-}
-
-struct UpRows {       // pyrUp rows rho(k-1), k, rho(k+1) for the lane's 4 columns, u and v
-    H4 u0, u1, u2, v0, v1, v2;
-};
+struct RawRow { double s0, s1, se; };       // coarse values j0, j0+1 and (lane 0: j0-1, lane 31: j0+2)
 
 struct UpCtx {
     const double* __restrict__ cu;
@@ -147,6 +114,69 @@ struct UpCtx {
     bool col_ok, edge;
 };
 
+// Issues the global loads of one coarse row (no use of the results: they can stay in flight).
+__device__ __forceinline__ RawRow raw_load(const double* __restrict__ row, const UpCtx& c)
+{
+    const int lane = threadIdx.x & 31;
+    RawRow r;
+    r.s0 = r.s1 = r.se = 0.0;
+    if (c.col_ok) {
+        if (c.j0 + 1 < c.wc) {
+            const double2 t = __ldg(reinterpret_cast<const double2*>(row + c.j0));
+            r.s0 = t.x;
+            r.s1 = t.y;
+        } else {
+            r.s0 = __ldg(row + c.j0);
+        }
+        if (lane == 0 && c.j0 > 0) r.se = __ldg(row + c.j0 - 1);
+        if (lane == 31 && c.j0 + 2 < c.wc) r.se = __ldg(row + c.j0 + 2);
+    }
+    return r;
+}
+
+__device__ __forceinline__ H4 hrow_finish(const RawRow& r, const UpCtx& c)
+{
+    const int lane = threadIdx.x & 31;
+    const int n = c.wc, j0 = c.j0;
+    const double s0 = r.s0, s1 = r.s1;
+    double sl = __shfl_up_sync(0xffffffffu, s1, 1);
+    double sr = __shfl_down_sync(0xffffffffu, s0, 1);
+    if (lane == 0) sl = r.se;
+    if (lane == 31) sr = r.se;
+    H4 h;
+    h.v[0] = dadd(dadd(sl, dmul(s0, 6.0)), s1);
+    h.v[1] = dmul(dadd(s0, s1), 4.0);
+    h.v[2] = dadd(dadd(s0, dmul(s1, 6.0)), sr);
+    h.v[3] = dmul(dadd(s1, sr), 4.0);
+    if (c.edge) {                                 // warp-uniform: only strips touching a border
+        if (c.xb == 0) h.v[0] = dadd(dmul(s0, 6.0), dmul(s1, 2.0));
+        if (j0 + 1 == n - 1) { h.v[2] = dadd(s0, dmul(s1, 7.0)); h.v[3] = dmul(s1, 8.0); }
+        if (j0 == n - 1) { h.v[0] = dadd(sl, dmul(s0, 7.0)); h.v[1] = dmul(s0, 8.0); }
+    }
+    return h;
+}
+
+__device__ __forceinline__ H4 pyrup_hrow4(const double* __restrict__ row, const UpCtx& c)
+{
+    return hrow_finish(raw_load(row, c), c);
+}
+
+struct UpRows {       // pyrUp rows rho(k-1), k, rho(k+1) for the lane's 4 columns, u and v
+    H4 u0, u1, u2, v0, v1, v2;
+};
+
+// Requests the coarse row the step after `k` will need into L1 (no destination registers), so
+// that its latency overlaps the gathers of the current row.
+__device__ __forceinline__ void up_prefetch(UpRows& r, const UpCtx& c, int knext)
+{
+    (void)r;
+    if (c.col_ok) {
+        const size_t o2 = (size_t)pyrup_rho(knext + 1, c.hc) * c.cp + c.j0;
+        prefetch_l1(c.cu + o2);
+        prefetch_l1(c.cv + o2);
+    }
+}
+
 __device__ __forceinline__ void up_advance(UpRows& r, const UpCtx& c, int k, int kprev)
 {
     if (k == kprev + 1) {
@@ -154,14 +184,15 @@ __device__ __forceinline__ void up_advance(UpRows& r, const UpCtx& c, int k, int
         r.v0 = r.v1; r.v1 = r.v2;
     } else {
         const size_t o0 = (size_t)pyrup_rho(k - 1, c.hc) * c.cp, o1 = (size_t)k * c.cp;
-        r.u0 = pyrup_hrow4(c.cu + o0, c.j0, c.wc, c.col_ok, c.xb, c.edge);
-        r.v0 = pyrup_hrow4(c.cv + o0, c.j0, c.wc, c.col_ok, c.xb, c.edge);
-        r.u1 = pyrup_hrow4(c.cu + o1, c.j0, c.wc, c.col_ok, c.xb, c.edge);
-        r.v1 = pyrup_hrow4(c.cv + o1, c.j0, c.wc, c.col_ok, c.xb, c.edge);
+        r.u0 = pyrup_hrow4(c.cu + o0, c);
+        r.v0 = pyrup_hrow4(c.cv + o0, c);
+        r.u1 = pyrup_hrow4(c.cu + o1, c);
+        r.v1 = pyrup_hrow4(c.cv + o1, c);
     }
     const size_t o2 = (size_t)pyrup_rho(k + 1, c.hc) * c.cp;
-    r.u2 = pyrup_hrow4(c.cu + o2, c.j0, c.wc, c.col_ok, c.xb, c.edge);
-    r.v2 = pyrup_hrow4(c.cv + o2, c.j0, c.wc, c.col_ok, c.xb, c.edge);
+    const RawRow ru = raw_load(c.cu + o2, c), rv = raw_load(c.cv + o2, c);
+    r.u2 = hrow_finish(ru, c);
+    r.v2 = hrow_finish(rv, c);
 }
 
 // Vertical pass of cv::pyrUp.  ((a+b)*4)*(1/64) == (a+b)*(1/16): both scalings are exact.
@@ -183,39 +214,36 @@ __device__ __forceinline__ void up_eval(const UpRows& r, int y, double (&upu)[4]
 }
 
 // ------------------------------------------------------------------------------ producers
-// OpenCV remap fixed-point coordinate, without the int16 saturation of q5(): with images of at
-// most 32767 pixels per side an unsaturated out-of-range coordinate stays out of range.  NaN
-// maps far outside (fmaxf returns the non-NaN operand), like cvRound's INT_MIN.
-__device__ __forceinline__ int q5s(float m)
-{
-    const float t = fminf(fmaxf(__fmul_rn(m, 32.0f), -1073741824.0f), 1073741824.0f);
-    return __float2int_rn(t);
-}
+// OpenCV remap fixed-point coordinate for a FINITE map value: s = rint(m * 32.f); F2I saturates,
+// and with images of at most 32767 pixels per side a saturated coordinate is out of range like
+// the unsaturated one.  Non-finite map values never get here (they take the per-tap path, q5()).
+__device__ __forceinline__ int q5s(float m) { return __float2int_rn(__fmul_rn(m, 32.0f)); }
 
 struct Tap {
-    int off;          // element offset of tap (iy, ix), clamped to (0,0) when not interior
-    int ax, ay;       // 5-bit fractions
-    bool interior;    // all four taps inside the image
+    int off;          // element offset of tap (iy, ix), 0 when not interior
+    int fr;           // ax | ay << 8 | interior << 16   (5-bit fractions)
 };
 
-__device__ __forceinline__ Tap make_tap(float mx, float my, int w, int h, int pitch)
+__device__ __forceinline__ Tap make_tap(float mx, float my, int w, int h, int pitch, bool finite)
 {
     const int sx = q5s(mx), sy = q5s(my);
     const int ix = sx >> 5, iy = sy >> 5;
+    const bool interior = finite && (unsigned)ix < (unsigned)(w - 1) && (unsigned)iy < (unsigned)(h - 1);
     Tap t;
-    t.ax = sx & 31;
-    t.ay = sy & 31;
-    t.interior = (unsigned)ix < (unsigned)(w - 1) && (unsigned)iy < (unsigned)(h - 1);
-    t.off = t.interior ? iy * pitch + ix : 0;
+    t.fr = (sx & 31) | ((sy & 31) << 8) | (interior ? 0x10000 : 0);
+    t.off = interior ? iy * pitch + ix : 0;
     return t;
 }
 
-__device__ __forceinline__ double blend4(double s00, double s01, double s10, double s11, int ax, int ay)
+__device__ __forceinline__ double blend4(double s00, double s01, double s10, double s11, int fr)
 {
-    const double w00 = q10_to_double((32 - ay) * (32 - ax));
-    const double w01 = q10_to_double((32 - ay) * ax);
-    const double w10 = q10_to_double(ay * (32 - ax));
-    const double w11 = q10_to_double(ay * ax);
+    const int ax = fr & 31, ay = (fr >> 8) & 31;
+    const int k11 = ay * ax;
+    const int k01 = 32 * ax - k11;                 // (32 - ay) * ax
+    const int k10 = 32 * ay - k11;                 // ay * (32 - ax)
+    const int k00 = 1024 - 32 * ax - k10;          // (32 - ay) * (32 - ax)
+    const double w00 = q10_to_double(k00), w01 = q10_to_double(k01);
+    const double w10 = q10_to_double(k10), w11 = q10_to_double(k11);
     return dadd(dadd(dadd(dmul(s00, w00), dmul(s01, w01)), dmul(s10, w10)), dmul(s11, w11));
 }
 
@@ -269,35 +297,56 @@ __device__ __forceinline__ void producer_role(const LevelArgs& a, const Geo& g, 
                 m1y = __fadd_rn(yf, hv);
                 m2x = __fsub_rn(xfi, hu);
                 m2y = __fsub_rn(yf, hv);
-                ta[i] = make_tap(m1x, m1y, W, H, pitch);
-                tb[i] = make_tap(m2x, m2y, W, H, pitch);
-                all_in = all_in && ta[i].interior && tb[i].interior;
+                const bool finite = fabsf(hu) + fabsf(hv) < __int_as_float(0x7f800000);
+                ta[i] = make_tap(m1x, m1y, W, H, pitch, finite);
+                tb[i] = make_tap(m2x, m2y, W, H, pitch, finite);
+                all_in = all_in && ((ta[i].fr & tb[i].fr) & 0x10000);
             }
-            // 32 independent gathers per lane, issued before the first use
-            double sa[4][4], sb[4][4];
+            // Gathers: 16 per frame per lane.  Frame 2's cache lines are requested first with L1
+            // prefetches (no destination registers), then frame 1's 16 loads are issued back to
+            // back and blended, then frame 2's (now near) loads.
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
-                const double* pa = A + ta[i].off;
                 const double* pb = B + tb[i].off;
-                sa[i][0] = __ldg(pa); sa[i][1] = __ldg(pa + 1);
-                sa[i][2] = __ldg(pa + pitch); sa[i][3] = __ldg(pa + pitch + 1);
-                sb[i][0] = __ldg(pb); sb[i][1] = __ldg(pb + 1);
-                sb[i][2] = __ldg(pb + pitch); sb[i][3] = __ldg(pb + pitch + 1);
+                prefetch_l1(pb);
+                prefetch_l1(pb + 1);
+                prefetch_l1(pb + pitch);
+                prefetch_l1(pb + pitch + 1);
             }
+            up_prefetch(up, uc, k + 1);               // coarse row of this producer's next step
+            {
+                double sa[4][4];
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                va[i] = blend4(sa[i][0], sa[i][1], sa[i][2], sa[i][3], ta[i].ax, ta[i].ay);
-                vb[i] = blend4(sb[i][0], sb[i][1], sb[i][2], sb[i][3], tb[i].ax, tb[i].ay);
+                for (int i = 0; i < 4; ++i) {
+                    const double* pa = A + ta[i].off;
+                    sa[i][0] = __ldg(pa); sa[i][1] = __ldg(pa + 1);
+                    sa[i][2] = __ldg(pa + pitch); sa[i][3] = __ldg(pa + pitch + 1);
+                }
+#pragma unroll
+                for (int i = 0; i < 4; ++i) va[i] = blend4(sa[i][0], sa[i][1], sa[i][2], sa[i][3], ta[i].fr);
+            }
+            {
+                double sb[4][4];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const double* pb = B + tb[i].off;
+                    sb[i][0] = __ldg(pb); sb[i][1] = __ldg(pb + 1);
+                    sb[i][2] = __ldg(pb + pitch); sb[i][3] = __ldg(pb + pitch + 1);
+                }
+#pragma unroll
+                for (int i = 0; i < 4; ++i) vb[i] = blend4(sb[i][0], sb[i][1], sb[i][2], sb[i][3], tb[i].fr);
             }
             if (!all_in && col_ok) {
                 // rare: a tap outside the image -> BORDER_CONSTANT 0 tested per tap
+                double upu2[4], upv2[4];
+                up_eval(up, yy, upu2, upv2);
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
-                    if (!(ta[i].interior && tb[i].interior)) {
+                    if (!((ta[i].fr & tb[i].fr) & 0x10000)) {
                         float m1x, m1y, m2x, m2y;
-                        map_coords(xb + i, yy, upu[i], upv[i], m1x, m1y, m2x, m2y);
-                        if (!ta[i].interior) va[i] = remap_tap4(A, a.img_pitch, W, H, m1x, m1y);
-                        if (!tb[i].interior) vb[i] = remap_tap4(B, a.img_pitch, W, H, m2x, m2y);
+                        map_coords(xb + i, yy, upu2[i], upv2[i], m1x, m1y, m2x, m2y);
+                        if (!(ta[i].fr & 0x10000)) va[i] = remap_tap4(A, a.img_pitch, W, H, m1x, m1y);
+                        if (!(tb[i].fr & 0x10000)) vb[i] = remap_tap4(B, a.img_pitch, W, H, m2x, m2y);
                     }
                 }
             }
@@ -536,10 +585,18 @@ __device__ __forceinline__ void consumer_role(const LevelArgs& a, const Geo& g, 
                 const double fyb = dadd(dsub(b10, sb), b11);
                 const double fta = -dadd(dadd(sa, a10), a11);
                 const double ftb = dadd(dadd(sb, b10), b11);
-                const bool in = (unsigned)(xb + i) < (unsigned)W;
-                fx[i] = in ? dadd(fxa, fxb) : 0.0;
-                fy[i] = in ? dadd(fya, fyb) : 0.0;
-                ft[i] = in ? dadd(fta, ftb) : 0.0;
+                fx[i] = dadd(fxa, fxb);
+                fy[i] = dadd(fya, fyb);
+                ft[i] = dadd(fta, ftb);
+            }
+            if (g.edge) {                            // columns outside the image contribute nothing
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const bool in = (unsigned)(xb + i) < (unsigned)W;
+                    fx[i] = in ? fx[i] : 0.0;
+                    fy[i] = in ? fy[i] : 0.0;
+                    ft[i] = in ? ft[i] : 0.0;
+                }
             }
 #pragma unroll
             for (int i = 0; i < 4; ++i) { prevA[i] = curA[i]; prevB[i] = curB[i]; }
@@ -552,10 +609,12 @@ __device__ __forceinline__ void consumer_role(const LevelArgs& a, const Geo& g, 
 
         const bool emit = n >= C::WIN - 1;
         const bool last = ib == C::WIN - 1;
-        double S[5][4];
+        // Horizontal sums of the five products for all lanes, in uniform control flow (the
+        // shuffles of the five channels interleave freely).
+        double h[5][4];
 #pragma unroll
         for (int c = 0; c < 5; ++c) {
-            double x[4], h[4];
+            double x[4];
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
                 // fx2, fy2, fxfy, fxft, fyft (:383-405)
@@ -563,48 +622,50 @@ __device__ __forceinline__ void consumer_role(const LevelArgs& a, const Geo& g, 
                 const double q = c == 0 ? fx[i] : (c <= 2 ? fy[i] : ft[i]);
                 x[i] = dmul(p, q);
             }
-            hsum4<R>(x, h);
-            if (active) {
-                // vertical van Herk / Gil-Werman: P = running prefix of the current block,
-                // the ring holds the suffix sums of the previous block, overwritten row by row.
-                double* vrow = vp + c * C::OUT_COLS;             // slot ib  <-> block row ib+1
-                if (ib == 0) {
+            hsum4<R>(x, h[c]);
+        }
+        // Vertical van Herk / Gil-Werman: P = running prefix of the current block (reset to 0
+        // when a block ends; 0 + h == h), the ring holds the suffix sums of the previous block,
+        // overwritten row by row.  Only loads and stores are predicated -- no divergent branch.
+        const bool ld_suf = active && !last;          // block row WIN-1: the window is the block itself
+        const bool st_raw = active && ib >= 1;
+        double S[5][4];
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) P[c][i] = h[i];
-                } else {
+        for (int c = 0; c < 5; ++c) {
+            double* vrow = vp + c * C::OUT_COLS;                 // slot ib  <-> block row ib+1
+            double sp[4] = {0.0, 0.0, 0.0, 0.0};
+            if (ld_suf) ld4s(vrow, C::HALF, sp);                 // suffix of previous block from row ib+1
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) P[c][i] = dadd(P[c][i], h[i]);
-                }
-                if (emit && !last) {
-                    double sp[4];
-                    ld4s(vrow, C::HALF, sp);                     // suffix of previous block from row ib+1
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) S[c][i] = dadd(sp[i], P[c][i]);
-                } else {
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) S[c][i] = P[c][i];
-                }
-                if (ib >= 1) st4s(vrow - C::VROW, C::HALF, h);   // raw row ib -> slot ib-1
+            for (int i = 0; i < 4; ++i) {
+                P[c][i] = dadd(P[c][i], h[c][i]);
+                S[c][i] = dadd(sp[i], P[c][i]);
             }
+            if (st_raw) st4s(vrow - C::VROW, C::HALF, h[c]);     // raw row ib -> slot ib-1
         }
 
-        if (last && active) {
-            // block finished: turn the stored raw rows 1..2R into suffix sums, in place
+        if (last) {
+            if (active) {
+                // block finished: turn the stored raw rows 1..2R into suffix sums, in place
 #pragma unroll
-            for (int c = 0; c < 5; ++c) {
-                double acc[4];
-                double* vr = v_lane + (C::VSLOTS - 1) * C::VROW + c * C::OUT_COLS;
-                ld4s(vr, C::HALF, acc);
+                for (int c = 0; c < 5; ++c) {
+                    double acc[4];
+                    double* vr = v_lane + (C::VSLOTS - 1) * C::VROW + c * C::OUT_COLS;
+                    ld4s(vr, C::HALF, acc);
 #pragma unroll 2
-                for (int t = C::VSLOTS - 2; t >= 0; --t) {
-                    vr -= C::VROW;
-                    double raw[4];
-                    ld4s(vr, C::HALF, raw);
+                    for (int t = C::VSLOTS - 2; t >= 0; --t) {
+                        vr -= C::VROW;
+                        double raw[4];
+                        ld4s(vr, C::HALF, raw);
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) acc[i] = dadd(raw[i], acc[i]);
-                    st4s(vr, C::HALF, acc);
+                        for (int i = 0; i < 4; ++i) acc[i] = dadd(raw[i], acc[i]);
+                        st4s(vr, C::HALF, acc);
+                    }
                 }
             }
+#pragma unroll
+            for (int c = 0; c < 5; ++c)
+#pragma unroll
+                for (int i = 0; i < 4; ++i) P[c][i] = 0.0;
         }
 
         if (emit) {
@@ -612,39 +673,38 @@ __device__ __forceinline__ void consumer_role(const LevelArgs& a, const Geo& g, 
             const int y = g.y0 + m;
             const int eslot = m & (NE - 1);
             if (m >= NE) bar_sync(BAR_LK_EMPTY + eslot, 64);
-            if (active) {
-                const bool yin = y >= R && y <= H - 1 - R;
-                double lu[4], lv[4], nus[4], nvs[4], dets[4];
-                unsigned okbits = 0;
-                bool fast = true;
+            const bool yin = y >= R && y <= H - 1 - R;
+            double lu[4], lv[4], nus[4], nvs[4], dets[4];
+            unsigned okbits = 0;
+            bool fast = true;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int x = xb + i;
+                const bool interior = yin && x >= R && x <= W - 1 - R;
+                const double sxx = S[0][i], syy = S[1][i], sxy = S[2][i], sxt = S[3][i], syt = S[4][i];
+                dets[i] = dsub(dmul(sxx, syy), dmul(sxy, sxy));
+                nus[i] = dsub(dmul(sxy, syt), dmul(syy, sxt));
+                nvs[i] = dsub(dmul(sxt, sxy), dmul(sxx, syt));
+                const bool ok = interior && fabs(dets[i]) > det_eps;
+                okbits |= ok ? (1u << (8 * i)) : 0u;
+                fast = (div2_fast(nus[i], nvs[i], dets[i], lu[i], lv[i]) || !ok) && fast;
+            }
+            if (!fast) {                             // rare: exponent range outside the fast path
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
-                    const int x = xb + i;
-                    const bool interior = yin && x >= R && x <= W - 1 - R;
-                    const double sxx = S[0][i], syy = S[1][i], sxy = S[2][i], sxt = S[3][i], syt = S[4][i];
-                    const double det = dsub(dmul(sxx, syy), dmul(sxy, sxy));
-                    const double nu = dsub(dmul(sxy, syt), dmul(syy, sxt));
-                    const double nv = dsub(dmul(sxt, sxy), dmul(sxx, syt));
-                    const bool ok = interior && fabs(det) > det_eps;
-                    dets[i] = ok ? det : 1.0;
-                    nus[i] = ok ? nu : 1.0;
-                    nvs[i] = ok ? nv : 1.0;
-                    okbits |= ok ? (1u << (8 * i)) : 0u;
-                    fast = div2_fast(nus[i], nvs[i], dets[i], lu[i], lv[i]) && fast;
-                }
-                if (!fast) {                         // rare: exponent range outside the fast path
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) {
+                    if ((okbits >> (8 * i)) & 1u) {
                         lu[i] = ddiv_slow(nus[i], dets[i]);
                         lv[i] = ddiv_slow(nvs[i], dets[i]);
                     }
                 }
+            }
 #pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    const bool ok = (okbits >> (8 * i)) & 1u;
-                    lu[i] = ok ? lu[i] : 0.0;
-                    lv[i] = ok ? lv[i] : 0.0;
-                }
+            for (int i = 0; i < 4; ++i) {
+                const bool ok = (okbits >> (8 * i)) & 1u;
+                lu[i] = ok ? lu[i] : 0.0;
+                lv[i] = ok ? lv[i] : 0.0;
+            }
+            if (active) {
                 double* lk = lk_lane + eslot * 2 * C::OUT_COLS;
                 st4s(lk, C::HALF, lu);
                 st4s(lk + C::OUT_COLS, C::HALF, lv);
@@ -697,7 +757,10 @@ __device__ __forceinline__ void epilogue_role(const LevelArgs& a, const Geo& g, 
         double upu[4], upv[4];
         if (g.has_coarse) {                          // upsampled coarse flow first (global loads)
             const int k = y >> 1;
-            if (k != kprev) up_advance(up, uc, k, kprev);
+            if (k != kprev) {
+                up_advance(up, uc, k, kprev);
+                up_prefetch(up, uc, k + 1);
+            }
             kprev = k;
             up_eval(up, y, upu, upv);
         }
