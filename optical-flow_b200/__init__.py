@@ -19,7 +19,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libof_b200.so")
+LIB_PATH = os.environ.get("OF_B200_LIB") or os.path.join(_HERE, "libof_b200.so")   # env: A/B builds (development)
 
 OF_OK, OF_E_BADARG, OF_E_NOT_DIVISIBLE, OF_E_CUDA, OF_E_NOMEM = 0, 1, 2, 3, 4
 

@@ -83,7 +83,6 @@ struct Geo {          // per-CTA geometry, identical in all roles
     bool edge;        // strip touches the left or right image border (pyrUp border formulas)
 };
 
-__device__ __forceinline__ void prefetch_l1(const double* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
 __device__ __forceinline__ double2 lds2(const double* p) { return *reinterpret_cast<const double2*>(p); }
 __device__ __forceinline__ void sts2(double* p, double x, double y) { *reinterpret_cast<double2*>(p) = make_double2(x, y); }
 
@@ -156,25 +155,37 @@ __device__ __forceinline__ H4 hrow_finish(const RawRow& r, const UpCtx& c)
     return h;
 }
 
-__device__ __forceinline__ H4 pyrup_hrow4(const double* __restrict__ row, const UpCtx& c)
+// Used by the (cold) full reload of the three rows.  (Measured: moving it out of line costs 16 %.)
+__device__ __forceinline__ H4 pyrup_hrow4(const double* __restrict__ row, int j0, int xb, int wc, bool col_ok, bool edge)
 {
+    UpCtx c;
+    c.cu = c.cv = nullptr;
+    c.cp = 0;
+    c.wc = wc;
+    c.hc = 0;
+    c.j0 = j0;
+    c.xb = xb;
+    c.col_ok = col_ok;
+    c.edge = edge;
     return hrow_finish(raw_load(row, c), c);
 }
 
 struct UpRows {       // pyrUp rows rho(k-1), k, rho(k+1) for the lane's 4 columns, u and v
     H4 u0, u1, u2, v0, v1, v2;
+    RawRow pu, pv;    // coarse row rho(pk + 1), loads possibly still in flight
+    int pk;           // k the prefetch was issued for (-100: none)
 };
 
-// Requests the coarse row the step after `k` will need into L1 (no destination registers), so
-// that its latency overlaps the gathers of the current row.
+// Issues the loads of the coarse row the step after `k` will need and leaves them in flight in
+// registers, so that their latency overlaps the gathers of the current row.  (Measured: an L1
+// prefetch instruction instead is slower than no prefetch at all -- L1 is tiny next to 225 KB of
+// shared memory.)
 __device__ __forceinline__ void up_prefetch(UpRows& r, const UpCtx& c, int knext)
 {
-    (void)r;
-    if (c.col_ok) {
-        const size_t o2 = (size_t)pyrup_rho(knext + 1, c.hc) * c.cp + c.j0;
-        prefetch_l1(c.cu + o2);
-        prefetch_l1(c.cv + o2);
-    }
+    const size_t o2 = (size_t)pyrup_rho(knext + 1, c.hc) * c.cp;
+    r.pu = raw_load(c.cu + o2, c);
+    r.pv = raw_load(c.cv + o2, c);
+    r.pk = knext;
 }
 
 __device__ __forceinline__ void up_advance(UpRows& r, const UpCtx& c, int k, int kprev)
@@ -184,15 +195,14 @@ __device__ __forceinline__ void up_advance(UpRows& r, const UpCtx& c, int k, int
         r.v0 = r.v1; r.v1 = r.v2;
     } else {
         const size_t o0 = (size_t)pyrup_rho(k - 1, c.hc) * c.cp, o1 = (size_t)k * c.cp;
-        r.u0 = pyrup_hrow4(c.cu + o0, c);
-        r.v0 = pyrup_hrow4(c.cv + o0, c);
-        r.u1 = pyrup_hrow4(c.cu + o1, c);
-        r.v1 = pyrup_hrow4(c.cv + o1, c);
+        r.u0 = pyrup_hrow4(c.cu + o0, c.j0, c.xb, c.wc, c.col_ok, c.edge);
+        r.v0 = pyrup_hrow4(c.cv + o0, c.j0, c.xb, c.wc, c.col_ok, c.edge);
+        r.u1 = pyrup_hrow4(c.cu + o1, c.j0, c.xb, c.wc, c.col_ok, c.edge);
+        r.v1 = pyrup_hrow4(c.cv + o1, c.j0, c.xb, c.wc, c.col_ok, c.edge);
     }
-    const size_t o2 = (size_t)pyrup_rho(k + 1, c.hc) * c.cp;
-    const RawRow ru = raw_load(c.cu + o2, c), rv = raw_load(c.cv + o2, c);
-    r.u2 = hrow_finish(ru, c);
-    r.v2 = hrow_finish(rv, c);
+    if (r.pk != k) up_prefetch(r, c, k);
+    r.u2 = hrow_finish(r.pu, c);
+    r.v2 = hrow_finish(r.pv, c);
 }
 
 // Vertical pass of cv::pyrUp.  ((a+b)*4)*(1/64) == (a+b)*(1/16): both scalings are exact.
@@ -247,6 +257,19 @@ __device__ __forceinline__ double blend4(double s00, double s01, double s10, dou
     return dadd(dadd(dadd(dmul(s00, w00), dmul(s01, w01)), dmul(s10, w10)), dmul(s11, w11));
 }
 
+// Rare path of the producers: a pixel with a tap outside the image (BORDER_CONSTANT 0 tested
+// per tap) or a non-finite map value.
+__device__ __forceinline__ double2 remap_cold(const double* __restrict__ A, const double* __restrict__ B, size_t pitch,
+                                           int W, int H, int x, int y, double upu, double upv,
+                                           double va, double vb, int fra, int frb)
+{
+    float m1x, m1y, m2x, m2y;
+    map_coords(x, y, upu, upv, m1x, m1y, m2x, m2y);
+    if (!(fra & 0x10000)) va = remap_tap4(A, pitch, W, H, m1x, m1y);
+    if (!(frb & 0x10000)) vb = remap_tap4(B, pitch, W, H, m2x, m2y);
+    return make_double2(va, vb);
+}
+
 template <int R>
 __device__ __forceinline__ void producer_role(const LevelArgs& a, const Geo& g, int pair, double* s_ab, int par)
 {
@@ -271,6 +294,7 @@ __device__ __forceinline__ void producer_role(const LevelArgs& a, const Geo& g, 
     uc.col_ok = col_ok;
     uc.edge = g.edge;
     UpRows up;
+    up.pk = -100;
     int kprev = -100;
     const float xf = (float)xb;
 
@@ -302,18 +326,8 @@ __device__ __forceinline__ void producer_role(const LevelArgs& a, const Geo& g, 
                 tb[i] = make_tap(m2x, m2y, W, H, pitch, finite);
                 all_in = all_in && ((ta[i].fr & tb[i].fr) & 0x10000);
             }
-            // Gathers: 16 per frame per lane.  Frame 2's cache lines are requested first with L1
-            // prefetches (no destination registers), then frame 1's 16 loads are issued back to
-            // back and blended, then frame 2's (now near) loads.
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const double* pb = B + tb[i].off;
-                prefetch_l1(pb);
-                prefetch_l1(pb + 1);
-                prefetch_l1(pb + pitch);
-                prefetch_l1(pb + pitch + 1);
-            }
-            up_prefetch(up, uc, k + 1);               // coarse row of this producer's next step
+            // Gathers: 16 per frame per lane, frame 1 issued back to back and blended, then frame 2.
+            // (All 32 at once needs 64 registers for the data in flight and spills.)
             {
                 double sa[4][4];
 #pragma unroll
@@ -322,6 +336,7 @@ __device__ __forceinline__ void producer_role(const LevelArgs& a, const Geo& g, 
                     sa[i][0] = __ldg(pa); sa[i][1] = __ldg(pa + 1);
                     sa[i][2] = __ldg(pa + pitch); sa[i][3] = __ldg(pa + pitch + 1);
                 }
+                up_prefetch(up, uc, k + 1);           // coarse row of this producer's next step
 #pragma unroll
                 for (int i = 0; i < 4; ++i) va[i] = blend4(sa[i][0], sa[i][1], sa[i][2], sa[i][3], ta[i].fr);
             }
@@ -343,10 +358,10 @@ __device__ __forceinline__ void producer_role(const LevelArgs& a, const Geo& g, 
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
                     if (!((ta[i].fr & tb[i].fr) & 0x10000)) {
-                        float m1x, m1y, m2x, m2y;
-                        map_coords(xb + i, yy, upu2[i], upv2[i], m1x, m1y, m2x, m2y);
-                        if (!(ta[i].fr & 0x10000)) va[i] = remap_tap4(A, a.img_pitch, W, H, m1x, m1y);
-                        if (!(tb[i].fr & 0x10000)) vb[i] = remap_tap4(B, a.img_pitch, W, H, m2x, m2y);
+                        const double2 f = remap_cold(A, B, a.img_pitch, W, H, xb + i, yy, upu2[i], upv2[i],
+                                                     va[i], vb[i], ta[i].fr, tb[i].fr);
+                        va[i] = f.x;
+                        vb[i] = f.y;
                     }
                 }
             }
@@ -646,6 +661,7 @@ __device__ __forceinline__ void consumer_role(const LevelArgs& a, const Geo& g, 
         if (last) {
             if (active) {
                 // block finished: turn the stored raw rows 1..2R into suffix sums, in place
+                // (the five channels advance together: 20 independent chains)
 #pragma unroll
                 for (int c = 0; c < 5; ++c) {
                     double acc[4];
@@ -748,6 +764,7 @@ __device__ __forceinline__ void epilogue_role(const LevelArgs& a, const Geo& g, 
     const double* lk_lane = s_lk + 2 * ol;
     const double mag2 = a.mag2_thresh;
     UpRows up;
+    up.pk = -100;
     int kprev = -100;
     unsigned long long st_x = 0, st_y = 0, st_c = 0;   // exact integer partial sums of this lane
     const int th = g.y1 - g.y0;
