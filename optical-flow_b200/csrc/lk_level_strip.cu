@@ -258,16 +258,11 @@ __device__ __forceinline__ double blend4(double s00, double s01, double s10, dou
 }
 
 // Rare path of the producers: a pixel with a tap outside the image (BORDER_CONSTANT 0 tested
-// per tap) or a non-finite map value.
-__device__ __forceinline__ double2 remap_cold(const double* __restrict__ A, const double* __restrict__ B, size_t pitch,
-                                           int W, int H, int x, int y, double upu, double upv,
-                                           double va, double vb, int fra, int frb)
+// per tap) or a non-finite map value.  Out of line: it must not widen the hot loop (the hot
+// loops of all roles have to fit the 32 KB instruction cache together).
+__device__ __noinline__ double remap_cold(const double* __restrict__ F, size_t pitch, int W, int H, float mx, float my)
 {
-    float m1x, m1y, m2x, m2y;
-    map_coords(x, y, upu, upv, m1x, m1y, m2x, m2y);
-    if (!(fra & 0x10000)) va = remap_tap4(A, pitch, W, H, m1x, m1y);
-    if (!(frb & 0x10000)) vb = remap_tap4(B, pitch, W, H, m2x, m2y);
-    return make_double2(va, vb);
+    return remap_tap4(F, pitch, W, H, mx, my);
 }
 
 template <int R>
@@ -301,77 +296,71 @@ __device__ __forceinline__ void producer_role(const LevelArgs& a, const Geo& g, 
     for (int d = par; d < g.n_deliv; d += 2) {
         const int yy = (d == 0) ? r101(g.vy_first - 1, H) : g.vy_first + d - 1;
         const int slot = d & (NB - 1);
-        double va[4], vb[4];
+        double* ra = s_ab + slot * AB_SLOT + 2 * lane;
         if (g.has_coarse) {
             const int k = yy >> 1;
             if (k != kprev) up_advance(up, uc, k, kprev);
             kprev = k;
-            double upu[4], upv[4];
-            up_eval(up, yy, upu, upv);
+            float hu[4], hv[4];                         // half flow, float32 (map build :667-684)
+            unsigned finite = 0;
+            {
+                double upu[4], upv[4];
+                up_eval(up, yy, upu, upv);
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    hu[i] = __fmul_rn(__double2float_rn(upu[i]), 0.5f);   // == f / 2 exactly
+                    hv[i] = __fmul_rn(__double2float_rn(upv[i]), 0.5f);
+                    finite |= (fabsf(hu[i]) + fabsf(hv[i]) < __int_as_float(0x7f800000)) ? (1u << i) : 0u;
+                }
+            }
             const float yf = (float)yy;
-            Tap ta[4], tb[4];
-            bool all_in = true;
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                float m1x, m1y, m2x, m2y;
-                const float fu = __double2float_rn(upu[i]), fv = __double2float_rn(upv[i]);
-                const float hu = __fmul_rn(fu, 0.5f), hv = __fmul_rn(fv, 0.5f);   // == f / 2 exactly
-                const float xfi = xf + (float)i;
-                m1x = __fadd_rn(xfi, hu);
-                m1y = __fadd_rn(yf, hv);
-                m2x = __fsub_rn(xfi, hu);
-                m2y = __fsub_rn(yf, hv);
-                const bool finite = fabsf(hu) + fabsf(hv) < __int_as_float(0x7f800000);
-                ta[i] = make_tap(m1x, m1y, W, H, pitch, finite);
-                tb[i] = make_tap(m2x, m2y, W, H, pitch, finite);
-                all_in = all_in && ((ta[i].fr & tb[i].fr) & 0x10000);
-            }
-            // Gathers: 16 per frame per lane, frame 1 issued back to back and blended, then frame 2.
-            // (All 32 at once needs 64 registers for the data in flight and spills.)
-            {
-                double sa[4][4];
+            // One pass per frame (rolled: the loop body is the hot code of this role): frame 1 is
+            // sampled at (x + hu, y + hv), frame 2 at (x - hu, y - hv); x - h == x + (-h) exactly.
+#pragma unroll 1
+            for (int f = 0; f < 2; ++f) {
+                const double* __restrict__ F = f ? B : A;
+                const float sg = f ? -1.0f : 1.0f;
+                Tap t[4];
+                unsigned all_in = 0x10000;
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
-                    const double* pa = A + ta[i].off;
-                    sa[i][0] = __ldg(pa); sa[i][1] = __ldg(pa + 1);
-                    sa[i][2] = __ldg(pa + pitch); sa[i][3] = __ldg(pa + pitch + 1);
+                    const float mx = __fadd_rn(xf + (float)i, __fmul_rn(sg, hu[i]));
+                    const float my = __fadd_rn(yf, __fmul_rn(sg, hv[i]));
+                    t[i] = make_tap(mx, my, W, H, pitch, (finite >> i) & 1u);
+                    all_in &= t[i].fr;
                 }
-                up_prefetch(up, uc, k + 1);           // coarse row of this producer's next step
-#pragma unroll
-                for (int i = 0; i < 4; ++i) va[i] = blend4(sa[i][0], sa[i][1], sa[i][2], sa[i][3], ta[i].fr);
-            }
-            {
-                double sb[4][4];
+                double sv[4][4];                        // 16 gathers per lane, issued back to back
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
-                    const double* pb = B + tb[i].off;
-                    sb[i][0] = __ldg(pb); sb[i][1] = __ldg(pb + 1);
-                    sb[i][2] = __ldg(pb + pitch); sb[i][3] = __ldg(pb + pitch + 1);
+                    const double* pa = F + t[i].off;
+                    sv[i][0] = __ldg(pa); sv[i][1] = __ldg(pa + 1);
+                    sv[i][2] = __ldg(pa + pitch); sv[i][3] = __ldg(pa + pitch + 1);
                 }
+                if (f == 0) up_prefetch(up, uc, k + 1);   // coarse row of this producer's next step
+                double v[4];
 #pragma unroll
-                for (int i = 0; i < 4; ++i) vb[i] = blend4(sb[i][0], sb[i][1], sb[i][2], sb[i][3], tb[i].fr);
-            }
-            if (!all_in && col_ok) {
-                // rare: a tap outside the image -> BORDER_CONSTANT 0 tested per tap
-                double upu2[4], upv2[4];
-                up_eval(up, yy, upu2, upv2);
+                for (int i = 0; i < 4; ++i) v[i] = blend4(sv[i][0], sv[i][1], sv[i][2], sv[i][3], t[i].fr);
+                if (!all_in && col_ok) {
 #pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    if (!((ta[i].fr & tb[i].fr) & 0x10000)) {
-                        const double2 f = remap_cold(A, B, a.img_pitch, W, H, xb + i, yy, upu2[i], upv2[i],
-                                                     va[i], vb[i], ta[i].fr, tb[i].fr);
-                        va[i] = f.x;
-                        vb[i] = f.y;
+                    for (int i = 0; i < 4; ++i) {
+                        if (!(t[i].fr & 0x10000)) {
+                            const float mx = __fadd_rn(xf + (float)i, __fmul_rn(sg, hu[i]));
+                            const float my = __fadd_rn(yf, __fmul_rn(sg, hv[i]));
+                            v[i] = remap_cold(F, a.img_pitch, W, H, mx, my);
+                        }
                     }
                 }
-            }
-            if (!col_ok) {
+                if (!col_ok) {
 #pragma unroll
-                for (int i = 0; i < 4; ++i) va[i] = vb[i] = 0.0;
-            } else if (!full4) {
-                va[2] = va[3] = vb[2] = vb[3] = 0.0;
+                    for (int i = 0; i < 4; ++i) v[i] = 0.0;
+                } else if (!full4) {
+                    v[2] = v[3] = 0.0;
+                }
+                if (f == 0 && d >= NB) bar_sync(BAR_AB_EMPTY + slot, 64);
+                st4s(ra + f * 128, 64, v);
             }
         } else {
+            double va[4], vb[4];
 #pragma unroll
             for (int i = 0; i < 4; ++i) va[i] = vb[i] = 0.0;
             if (col_ok) {
@@ -390,11 +379,10 @@ __device__ __forceinline__ void producer_role(const LevelArgs& a, const Geo& g, 
                         if (xb + i < W) { va[i] = __ldg(pa + i); vb[i] = __ldg(pb + i); }
                 }
             }
+            if (d >= NB) bar_sync(BAR_AB_EMPTY + slot, 64);
+            st4s(ra, 64, va);
+            st4s(ra + 128, 64, vb);
         }
-        if (d >= NB) bar_sync(BAR_AB_EMPTY + slot, 64);
-        double* ra = s_ab + slot * AB_SLOT + 2 * lane;
-        st4s(ra, 64, va);
-        st4s(ra + 128, 64, vb);
         bar_arrive(BAR_AB_FULL + slot, 64);
     }
 }
@@ -662,8 +650,8 @@ __device__ __forceinline__ void consumer_role(const LevelArgs& a, const Geo& g, 
             if (active) {
                 // block finished: turn the stored raw rows 1..2R into suffix sums, in place
                 // (the five channels advance together: 20 independent chains)
-#pragma unroll
-                for (int c = 0; c < 5; ++c) {
+#pragma unroll 1
+                for (int c = 0; c < 5; ++c) {                     // rolled: small code, runs once per block
                     double acc[4];
                     double* vr = v_lane + (C::VSLOTS - 1) * C::VROW + c * C::OUT_COLS;
                     ld4s(vr, C::HALF, acc);

@@ -8,7 +8,7 @@ src = open('/root/repo/optical-flow_b200/csrc/lk_level_strip.cu').read().split('
 def find(pat):
     return [i + 1 for i, l in enumerate(src) if re.search(pat, l)][0]
 b = [("producer", find(r"void producer_role")), ("helpers", find(r"// -+ consumer")),
-     ("consumer", find(r"void consumer_role")), ("epilogue", find(r"void epilogue_role")), ("kernel", find(r"lk_level_strip_kernel\("))]
+     ("consumer", find(r"void consumer_xx_role")), ("helpers", find(r"struct EpiCtx")), ("epilogue", find(r"void consumer_xt_role")), ("kernel", find(r"lk_level_strip_kernel\("))]
 def role_of(line):
     r = None
     for name, lo in b:
