@@ -6,13 +6,14 @@ import csv, io, subprocess, sys, re
 rep = sys.argv[1]
 src = open('/root/repo/optical-flow_b200/csrc/lk_level_strip.cu').read().split('\n')
 def find(pat):
-    return [i + 1 for i, l in enumerate(src) if re.search(pat, l)][0]
+    hits = [i + 1 for i, l in enumerate(src) if re.search(pat, l)]
+    return hits[0] if hits else 10 ** 9
 b = [("producer", find(r"void producer_role")), ("helpers", find(r"// -+ consumer")),
-     ("consumer", find(r"void consumer_xx_role")), ("helpers", find(r"struct EpiCtx")), ("epilogue", find(r"void consumer_xt_role")), ("kernel", find(r"lk_level_strip_kernel\("))]
+     ("consumer", min(find(r"void consumer_role"), find(r"void consumer_xx_role"))), ("epilogue", min(find(r"void epilogue_role"), find(r"void consumer_xt_role"))), ("kernel", find(r"lk_level_strip_kernel\("))]
 def role_of(line):
     r = None
     for name, lo in b:
-        if line >= lo: r = name
+        if line >= lo and lo < 10 ** 9: r = name
     return r
 out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-source", "cuda,sass"], capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(out)))
