@@ -21,6 +21,8 @@ cudaError_t launch_lk_level_tile(const LevelArgs& a, int n_pairs, cudaStream_t s
                                  unsigned long long* launches);
 cudaError_t launch_lk_level_march(const LevelArgs& a, int n_pairs, cudaStream_t s,
                                   unsigned long long* launches, bool* handled);
+cudaError_t launch_lk_level_phase(const LevelArgs& a, int n_pairs, cudaStream_t s,
+                                  unsigned long long* launches, bool* handled);
 cudaError_t launch_lk_level_strip(const LevelArgs& a, int n_pairs, cudaStream_t s,
                                   unsigned long long* launches, bool* handled);
 }  // namespace ofb
@@ -51,7 +53,7 @@ struct of_ctx {
     Arena staging;                     // device copies of host-pointer inputs/outputs
     std::string err;
     unsigned long long launches = 0;
-    int force_variant = 0;             // 0 auto, 1 tile, 2 march, 3 strip (test hook via OF_B200_VARIANT)
+    int force_variant = 0;             // 0 auto, 1 tile, 2 march, 3 strip, 4 phase (test hook via OF_B200_VARIANT)
     // optional per-launch device timing of the most recent batch call (bench roofline evidence)
     bool timing = false;
     std::vector<cudaEvent_t> tev;      // 2 events per timed launch
@@ -213,7 +215,12 @@ struct TimedLaunch {
 
 cudaError_t launch_lk_level(of_ctx* ctx, const ofb::LevelArgs& a, int n_pairs, cudaStream_t s)
 {
-    if (ctx->force_variant == 0 || ctx->force_variant == 3) {
+    if (ctx->force_variant == 4) {
+        bool handled = false;
+        cudaError_t e = ofb::launch_lk_level_phase(a, n_pairs, s, &ctx->launches, &handled);
+        if (handled || e != cudaSuccess) return e;
+    }
+    if (ctx->force_variant == 0 || ctx->force_variant == 3 || ctx->force_variant == 4) {
         bool handled = false;
         cudaError_t e = ofb::launch_lk_level_strip(a, n_pairs, s, &ctx->launches, &handled);
         if (handled || e != cudaSuccess) return e;
@@ -405,6 +412,7 @@ of_status of_ctx_create(int device, const of_params* params, of_ctx** out)
         if (!strcmp(fv, "tile")) ctx->force_variant = 1;
         else if (!strcmp(fv, "march")) ctx->force_variant = 2;
         else if (!strcmp(fv, "strip")) ctx->force_variant = 3;
+        else if (!strcmp(fv, "phase")) ctx->force_variant = 4;
     }
     e = cudaSetDevice(device);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);

@@ -4,12 +4,19 @@ Roles are contiguous SASS address regions; an instruction is classified by a maj
 role-specific source lines in a window around it."""
 import csv, io, subprocess, sys, re
 rep = sys.argv[1]
-src = open('/root/repo/optical-flow_b200/csrc/lk_level_strip.cu').read().split('\n')
+srcfile = sys.argv[2] if len(sys.argv) > 2 else "lk_level_strip.cu"
+src = open('/root/repo/optical-flow_b200/csrc/' + srcfile).read().split('\n')
 def find(pat):
     hits = [i + 1 for i, l in enumerate(src) if re.search(pat, l)]
     return hits[0] if hits else 10 ** 9
-b = [("producer", find(r"void producer_role")), ("helpers", find(r"// -+ consumer")),
-     ("consumer", min(find(r"void consumer_role"), find(r"void consumer_xx_role"))), ("epilogue", min(find(r"void epilogue_role"), find(r"void consumer_xt_role"))), ("kernel", find(r"lk_level_strip_kernel\("))]
+if len(sys.argv) > 3:      # role = function name pattern
+    b = [(p, find(r"void " + p)) for p in sys.argv[3:]]
+    ROLES = tuple(sys.argv[3:])
+else:
+    b = [("producer", find(r"void producer_role")), ("helpers", find(r"// -+ consumer")),
+         ("consumer", min(find(r"void consumer_role"), find(r"void consumer_xx_role"))), ("epilogue", min(find(r"void epilogue_role"), find(r"void consumer_xt_role"))), ("kernel", find(r"lk_level_strip_kernel\("))]
+    ROLES = ("producer", "consumer", "epilogue")
+b.sort(key=lambda x: x[1])
 def role_of(line):
     r = None
     for name, lo in b:
@@ -25,11 +32,12 @@ ins = []   # (addr, tag, op, n, s)
 for r in rows[hi + 1:]:
     if r and r[0] == "File Path": cur = r[1].split('/')[-1]; continue
     if len(r) <= ie: continue
+    if r[0] == "Line No": continue
     if r[0] != "":
         tag = None
-        if cur == "" or cur.endswith("lk_level_strip.cu"):
+        if cur == "" or cur.endswith(srcfile):
             rr = role_of(int(r[0]))
-            if rr in ("producer", "consumer", "epilogue"): tag = rr
+            if rr in ROLES: tag = rr
         continue
     t = r[3].split()
     op = (t[1] if t and t[0].startswith("@") else t[0]).split(".")[0] if t else "?"
@@ -41,7 +49,7 @@ for r in rows[hi + 1:]:
         except ValueError: st[x] = 0
     ins.append([int(r[2], 16), tag, op, n, s, st])
 ins.sort(key=lambda x: x[0])
-Wd = 60
+Wd = int(__import__('os').environ.get('ROLE_WIN', '60'))
 agg = {}
 for i, x in enumerate(ins):
     votes = {}

@@ -1,7 +1,9 @@
 #!/bin/bash
 # usage: tools/prof.sh <tag>  -- ncu --set full of the level-0 strip kernel on the GPU box, then digest here
 tag=$1
-/usr/local/graft/bin/gpurun --timeout 600 -- "ncu --set full --clock-control none --import-source on -k regex:lk_level_strip -s 2 -c 1 -o gpurun_out/$tag python bench.py --steps 1 --warmup 3 --pairs 16 --no-cpu-baseline > gpurun_out/ncu_full.log 2>&1; tail -1 gpurun_out/ncu_full.log | cut -c1-80" 2>&1 | tail -2
+kern=${2:-lk_level_strip}
+shift; shift
+/usr/local/graft/bin/gpurun --timeout 600 -- "OF_B200_VARIANT=${OF_B200_VARIANT:-} ncu --set full --clock-control none --import-source on -k regex:$kern -s 2 -c 1 -o gpurun_out/$tag python bench.py --steps 1 --warmup 3 --pairs 16 --no-cpu-baseline > gpurun_out/ncu_full.log 2>&1; tail -1 gpurun_out/ncu_full.log | cut -c1-80" 2>&1 | tail -2
 ncu -i gpurun_out/$tag.ncu-rep --page raw --csv 2>/dev/null | python -c "
 import csv,sys
 rows=list(csv.reader(sys.stdin))
@@ -20,4 +22,4 @@ for r in rows[2:]:
 mx=max(ex)
 print('static',len(ex),'max',mx,'hot(>30%max)',sum(1 for e in ex if e>0.3*mx),'warm(3-30%)',sum(1 for e in ex if 0.03*mx<e<=0.3*mx),'cold(<3%,>0)',sum(1 for e in ex if 0<e<=0.03*mx),'never',sum(1 for e in ex if e==0))
 "
-python tools/ncu_roles.py gpurun_out/$tag.ncu-rep | grep -E "==|stalls"
+python tools/ncu_roles.py gpurun_out/$tag.ncu-rep $kern.cu "$@" | grep -E "==|stalls"
