@@ -37,9 +37,9 @@ namespace ofb {
 
 namespace {
 
-constexpr int PH_NT = 640;       // threads per CTA: 128 columns x 5 channels in P3
-constexpr int PH_PC = 128;       // product columns per strip
-constexpr int PH_PITCH = 136;    // doubles per PROD row: lo pairs [0,64), hi pairs [72,136)
+constexpr int PH_NT = 512;       // threads per CTA (16 warps; a warp = one row of 32 quads)
+constexpr int PH_NW = PH_NT / 32;
+constexpr int PH_PC = 128;       // product columns per strip = 32 lanes x 4 columns
 
 template <int R>
 struct PhaseCfg {
@@ -50,17 +50,28 @@ struct PhaseCfg {
     static constexpr int WIN = 2 * R + 1;             // rows per step = vertical block length
     static constexpr int AB_ROWS = WIN + 1;           // + the row above the step
     static constexpr int HR_ROWS = (WIN + 1) / 2 + 3; // coarse rows a step can touch
-    static constexpr int PROD_D = WIN * 5 * PH_PITCH;
+    static constexpr int PROD_D = WIN * 5 * PH_PC;
     static constexpr int AB_D = AB_ROWS * 2 * PH_PC;
     static constexpr int HR_D = HR_ROWS * 2 * PH_PC;
-    static constexpr size_t SMEM_BYTES = (size_t)(PROD_D + AB_D + HR_D) * 8;
+    static constexpr int VS_D = 2 * R * 5 * PH_PC;    // suffix sums of the previous vertical block
+    static constexpr size_t SMEM_BYTES = (size_t)(PROD_D + AB_D + HR_D + VS_D) * 8;
+    static constexpr int VPAIRS = 2 * OUT_LANES;      // column pairs per channel in P3
 };
 
-// Position of strip column X (0..127) inside a PROD row.  Columns 4j, 4j+1 of lane j sit at
-// lo[2j], columns 4j+2, 4j+3 at hi[2j]; hi is skewed by 8 doubles so that both the
-// column-per-thread accesses (P2, P3, P4b) and the 4-columns-per-lane 128-bit accesses (P4a)
-// are bank-conflict-free.
-__device__ __forceinline__ int ppos(int X) { return ((X & 2) ? 72 : 0) + 2 * (X >> 2) + (X & 1); }
+// All shared-memory rows are "pair-split": columns 4j, 4j+1 of lane j sit at lo[2j], columns
+// 4j+2, 4j+3 at hi[2j] = row[64 + 2j], so that every 128-bit access of a warp is contiguous.
+__device__ __forceinline__ double2 lds2(const double* p) { return *reinterpret_cast<const double2*>(p); }
+__device__ __forceinline__ void sts2(double* p, double x, double y) { *reinterpret_cast<double2*>(p) = make_double2(x, y); }
+__device__ __forceinline__ void ld4s(const double* p, double (&v)[4])
+{
+    const double2 a = lds2(p), b = lds2(p + 64);
+    v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y;
+}
+__device__ __forceinline__ void st4s(double* p, const double (&v)[4])
+{
+    sts2(p, v[0], v[1]);
+    sts2(p + 64, v[2], v[3]);
+}
 
 struct PGeo {
     int W, H;
@@ -68,33 +79,77 @@ struct PGeo {
     int xo0;          // first output column
     int y0, y1;       // output rows [y0, y1)
     bool has_coarse;
+    bool edge;        // strip reaches outside the image on the left or right
+    bool vec_img, vec_uv, vec_c;   // 16-byte alignment of the image / flow / coarse-flow rows
 };
+
+// Position of strip column X inside a pair-split row.
+__device__ __forceinline__ int ppos(int X) { return ((X & 2) << 5) + 2 * (X >> 2) + (X & 1); }
 
 // ------------------------------------------------------------------------------ P0
 // Horizontal pass of cv::pyrUp (:646-647) of coarse rows rho(ka) .. rho(ka + nk - 1), both
-// flow planes, for the strip's 128 fine columns.  Columns outside the image hold 0.
-__device__ __forceinline__ void phase_up_rows(const LevelArgs& a, const PGeo& g, const double* __restrict__ cu,
-                                              const double* __restrict__ cv, int ka, int nk, double* s_hr)
+// flow planes, for the strip's 128 fine columns (plain layout); task = (row, plane, coarse
+// column j) -> fine columns 2j, 2j+1.  Columns outside the image hold 0.  Split in two so that
+// the global loads are in flight while the thread does other work: issue() starts the loads of
+// the thread's (at most UP_K) tasks, finish() forms the rows and stores them.
+constexpr int UP_K = 3;
+struct UpPre { double sm1[UP_K], s0[UP_K], s1[UP_K]; };
+
+template <int HR_ROWS>
+__device__ __forceinline__ void up_rows_issue(const LevelArgs& a, const PGeo& g, const double* __restrict__ cu,
+                                              const double* __restrict__ cv, int ka, int nk, UpPre& q)
+{
+    static_assert(UP_K * PH_NT >= HR_ROWS * PH_PC, "UP_K too small");
+    const int wc = a.wc, hc = a.hc;
+    const int j = (g.c0 >> 1) + (threadIdx.x & 63);
+    const int p = (threadIdx.x >> 6) & 1;
+    const double* plane = p ? cv : cu;
+    const bool interior = j >= 1 && j + 1 < wc;
+#pragma unroll
+    for (int k = 0; k < UP_K; ++k) {
+        const int r = (threadIdx.x >> 7) + k * (PH_NT / PH_PC);
+        q.sm1[k] = q.s0[k] = q.s1[k] = 0.0;
+        if (r < nk && interior) {
+            const double* row = plane + (size_t)pyrup_rho(ka + r, hc) * a.c_pitch + j;
+            q.sm1[k] = __ldg(row - 1);
+            q.s0[k] = __ldg(row);
+            q.s1[k] = __ldg(row + 1);
+        }
+    }
+}
+
+__device__ __forceinline__ void up_rows_finish(const LevelArgs& a, const PGeo& g, const double* __restrict__ cu,
+                                               const double* __restrict__ cv, int ka, int nk, const UpPre& q,
+                                               double* s_hr)
 {
     const int wc = a.wc, hc = a.hc;
-    for (int t = threadIdx.x; t < nk * 2 * PH_PC; t += PH_NT) {
-        const int X = t & (PH_PC - 1);
-        const int p = (t >> 7) & 1;
-        const int r = t >> 8;
-        const int gx = g.c0 + X;
-        double val = 0.0;
-        if ((unsigned)gx < (unsigned)g.W) {
-            const double* row = (p ? cv : cu) + (size_t)pyrup_rho(ka + r, hc) * a.c_pitch;
-            val = pyrup_row(row, 0, gx, wc);
+    const int jl = threadIdx.x & 63;
+    const int j = (g.c0 >> 1) + jl;
+    const int p = (threadIdx.x >> 6) & 1;
+    const bool interior = j >= 1 && j + 1 < wc;
+#pragma unroll
+    for (int k = 0; k < UP_K; ++k) {
+        const int r = (threadIdx.x >> 7) + k * (PH_NT / PH_PC);
+        if (r >= nk) continue;
+        double e = dadd(dadd(q.sm1[k], dmul(q.s0[k], 6.0)), q.s1[k]);
+        double o = dmul(dadd(q.s0[k], q.s1[k]), 4.0);
+        if (!interior) {
+            e = o = 0.0;
+            if ((unsigned)j < (unsigned)wc) {                // image border: cv::pyrUp's edge formulas
+                const double* row = (p ? cv : cu) + (size_t)pyrup_rho(ka + r, hc) * a.c_pitch;
+                e = pyrup_row(row, 0, 2 * j, wc);
+                o = pyrup_row(row, 0, 2 * j + 1, wc);
+            }
         }
-        s_hr[t] = val;
+        sts2(s_hr + (r * 2 + p) * PH_PC + 2 * jl, e, o);
     }
 }
 
 // ------------------------------------------------------------------------------ P1
 // Warped frames A', B' (:667-700) of fine rows vy0 + r - 1, r = r_lo .. WIN, into the AB block
-// (slot of r = (sb + r) mod AB_ROWS).  Row -1 is the reflect-101 row above row 0 (image row 1),
-// other rows outside the image are never read and are skipped.
+// (slot of r = (sb + r) mod AB_ROWS); one warp per row, a lane takes the columns lane + 32 i so
+// that every gather instruction of the warp reads 32 neighbouring pixels.  Row -1 is the
+// reflect-101 row above row 0 (image row 1); other rows outside the image are never read.
 template <int R>
 __device__ __forceinline__ void phase_remap(const LevelArgs& a, const PGeo& g, const double* __restrict__ A,
                                             const double* __restrict__ B, double* __restrict__ U,
@@ -104,88 +159,162 @@ __device__ __forceinline__ void phase_remap(const LevelArgs& a, const PGeo& g, c
     using C = PhaseCfg<R>;
     const int W = g.W, H = g.H;
     const int pitch = (int)a.img_pitch;
-    const int ntask = (C::WIN + 1 - r_lo) * PH_PC;
-    for (int t = threadIdx.x; t < ntask; t += PH_NT) {
-        const int X = t & (PH_PC - 1);
-        const int r = (t >> 7) + r_lo;
+    const int lane = threadIdx.x & 31;
+    for (int r = (threadIdx.x >> 5) + r_lo; r <= C::WIN; r += PH_NW) {
         const int vy = vy0 + r - 1;
         int yy = vy;
         if (vy == -1) yy = H > 1 ? 1 : 0;
         else if ((unsigned)vy >= (unsigned)H) continue;
         int slot = sb + r;
         if (slot >= C::AB_ROWS) slot -= C::AB_ROWS;
-        double* dst = s_ab + slot * (2 * PH_PC) + X;
-        const int gx = g.c0 + X;
-        double va = 0.0, vb = 0.0;
-        if ((unsigned)gx < (unsigned)W) {
-            if (g.has_coarse) {
-                const int k = yy >> 1;
-                const double* hu = s_hr + ((k - ka) * 2) * PH_PC + X;      // row k, plane u
-                const double* hv = hu + PH_PC;
-                double upu, upv;
-                if (yy & 1) {
-                    upu = dmul(dmul(dadd(hu[0], hu[2 * PH_PC]), 4.0), 1.0 / 64.0);
-                    upv = dmul(dmul(dadd(hv[0], hv[2 * PH_PC]), 4.0), 1.0 / 64.0);
-                } else {
-                    upu = dmul(dadd(dadd(hu[-2 * PH_PC], dmul(hu[0], 6.0)), hu[2 * PH_PC]), 1.0 / 64.0);
-                    upv = dmul(dadd(dadd(hv[-2 * PH_PC], dmul(hv[0], 6.0)), hv[2 * PH_PC]), 1.0 / 64.0);
-                }
-                // park the upsampled flow of output pixels for the epilogue (tmpu += upu, :634-637)
-                if (vy == yy && vy >= g.y0 && vy < g.y1 && gx >= g.xo0 && gx < g.xo0 + C::OUT_COLS) {
-                    U[(size_t)vy * a.uv_pitch + gx] = upu;
-                    V[(size_t)vy * a.uv_pitch + gx] = upv;
-                }
-                float m1x, m1y, m2x, m2y;
-                map_coords(gx, yy, upu, upv, m1x, m1y, m2x, m2y);
-                const bool finite = fabsf(m1x) + fabsf(m1y) + fabsf(m2x) + fabsf(m2y) < __int_as_float(0x7f800000);
-                const Tap t1 = make_tap(m1x, m1y, W, H, pitch, finite);
-                const Tap t2 = make_tap(m2x, m2y, W, H, pitch, finite);
-                const double* pa = A + t1.off;
-                const double* pb = B + t2.off;
-                const double a00 = __ldg(pa), a01 = __ldg(pa + 1), a10 = __ldg(pa + pitch), a11 = __ldg(pa + pitch + 1);
-                const double b00 = __ldg(pb), b01 = __ldg(pb + 1), b10 = __ldg(pb + pitch), b11 = __ldg(pb + pitch + 1);
-                va = blend4(a00, a01, a10, a11, t1.fr);
-                vb = blend4(b00, b01, b10, b11, t2.fr);
-                if (!(t1.fr & t2.fr & 0x10000)) {        // rare: a tap outside the image or a non-finite map
-                    if (!(t1.fr & 0x10000)) va = remap_tap4(A, a.img_pitch, W, H, m1x, m1y);
-                    if (!(t2.fr & 0x10000)) vb = remap_tap4(B, a.img_pitch, W, H, m2x, m2y);
+        double* dst = s_ab + slot * (2 * PH_PC);
+        double va[4] = {0.0, 0.0, 0.0, 0.0}, vb[4] = {0.0, 0.0, 0.0, 0.0};
+        const int x0 = g.c0 + lane;
+        unsigned inm = 0;                                    // columns of this lane inside the image
+#pragma unroll
+        for (int i = 0; i < 4; ++i) inm |= (unsigned)(x0 + 32 * i) < (unsigned)W ? (1u << i) : 0u;
+        if (g.has_coarse) {
+            // vertical pass of cv::pyrUp from the rows of P0
+            const int k = yy >> 1;
+            const double* hu = s_hr + ((k - ka) * 2) * PH_PC + lane;      // row k, plane u
+            double upu[4], upv[4];
+            if (yy & 1) {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const double* h = hu + 32 * i;
+                    upu[i] = dmul(dmul(dadd(h[0], h[2 * PH_PC]), 4.0), 1.0 / 64.0);
+                    upv[i] = dmul(dmul(dadd(h[PH_PC], h[3 * PH_PC]), 4.0), 1.0 / 64.0);
                 }
             } else {
-                va = __ldg(A + (size_t)yy * a.img_pitch + gx);
-                vb = __ldg(B + (size_t)yy * a.img_pitch + gx);
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const double* h = hu + 32 * i;
+                    upu[i] = dmul(dadd(dadd(h[-2 * PH_PC], dmul(h[0], 6.0)), h[2 * PH_PC]), 1.0 / 64.0);
+                    upv[i] = dmul(dadd(dadd(h[-PH_PC], dmul(h[PH_PC], 6.0)), h[3 * PH_PC]), 1.0 / 64.0);
+                }
             }
+            // park the upsampled flow of output pixels for the epilogue (tmpu += upu, :634-637)
+            if (vy == yy && vy >= g.y0 && vy < g.y1) {
+                double* pu = U + (size_t)vy * a.uv_pitch + x0;
+                double* pv = V + (size_t)vy * a.uv_pitch + x0;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const int X = lane + 32 * i;
+                    if (X >= 4 * C::HL && X < 4 * C::HL + C::OUT_COLS && ((inm >> i) & 1u)) {
+                        pu[32 * i] = upu[i];
+                        pv[32 * i] = upv[i];
+                    }
+                }
+            }
+            float hu4[4], hv4[4];                            // half flow, float32 (map build :667-684)
+            unsigned finite = 0;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                hu4[i] = __fmul_rn(__double2float_rn(upu[i]), 0.5f);          // == f / 2 exactly
+                hv4[i] = __fmul_rn(__double2float_rn(upv[i]), 0.5f);
+                finite |= (fabsf(hu4[i]) + fabsf(hv4[i]) < __int_as_float(0x7f800000)) ? (1u << i) : 0u;
+            }
+            const float xf = (float)x0, yf = (float)yy;
+            // frame 1 is sampled at (x + hu, y + hv), frame 2 at (x - hu, y - hv)
+#pragma unroll
+            for (int f = 0; f < 2; ++f) {
+                const double* __restrict__ F = f ? B : A;
+                Tap tp[4];
+                unsigned all_in = 0x10000;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const float xi = xf + (float)(32 * i);
+                    const float mx = f ? __fsub_rn(xi, hu4[i]) : __fadd_rn(xi, hu4[i]);
+                    const float my = f ? __fsub_rn(yf, hv4[i]) : __fadd_rn(yf, hv4[i]);
+                    tp[i] = make_tap(mx, my, W, H, pitch, (finite >> i) & 1u);
+                    all_in &= tp[i].fr | (((inm >> i) & 1u) ? 0u : 0x10000u);
+                }
+                double sv[4][4];                             // 16 gathers, issued back to back
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const double* pa = F + tp[i].off;
+                    sv[i][0] = __ldg(pa); sv[i][1] = __ldg(pa + 1);
+                    sv[i][2] = __ldg(pa + pitch); sv[i][3] = __ldg(pa + pitch + 1);
+                }
+                double* v = f ? vb : va;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) v[i] = blend4(sv[i][0], sv[i][1], sv[i][2], sv[i][3], tp[i].fr);
+                if (!all_in) {                               // rare: a tap outside the image, non-finite map
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        if (!(tp[i].fr & 0x10000) && ((inm >> i) & 1u)) {
+                            const float xi = xf + (float)(32 * i);
+                            const float mx = f ? __fsub_rn(xi, hu4[i]) : __fadd_rn(xi, hu4[i]);
+                            const float my = f ? __fsub_rn(yf, hv4[i]) : __fadd_rn(yf, hv4[i]);
+                            v[i] = remap_tap4(F, a.img_pitch, W, H, mx, my);
+                        }
+                    }
+                }
+            }
+        } else {
+            const double* pa = A + (size_t)yy * a.img_pitch + x0;
+            const double* pb = B + (size_t)yy * a.img_pitch + x0;
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+                if ((inm >> i) & 1u) { va[i] = __ldg(pa + 32 * i); vb[i] = __ldg(pb + 32 * i); }
         }
-        dst[0] = va;
-        dst[PH_PC] = vb;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const bool in = (inm >> i) & 1u;
+            const int q = ppos(lane + 32 * i);
+            dst[q] = in ? va[i] : 0.0;
+            dst[PH_PC + q] = in ? vb[i] : 0.0;
+        }
     }
 }
 
 // ------------------------------------------------------------------------------ P2
-// Gradients (2x2 filter2D stencils over both frames, accumulation order
-// ((k00 p00 + k01 p01) + k10 p10) + k11 p11, :44-84) and the five products (:383-405) of
-// product rows vy0 + i, i = 0 .. WIN-1.  Rows and columns outside the image contribute 0.
+// One warp per product row vy0 + i (lane = 4 consecutive columns): gradients (2x2 filter2D
+// stencils over both frames, accumulation order ((k00 p00 + k01 p01) + k10 p10) + k11 p11,
+// :44-84), the five products (:383-405) and their horizontal (2R+1)-column window sums in
+// registers + shuffles (additions only).  Rows and columns outside the image contribute 0.
 template <int R>
 __device__ __forceinline__ void phase_products(const PGeo& g, int vy0, int sb, const double* s_ab, double* s_prod)
 {
     using C = PhaseCfg<R>;
     const int W = g.W, H = g.H;
-    for (int t = threadIdx.x; t < C::WIN * PH_PC; t += PH_NT) {
-        const int X = t & (PH_PC - 1);
-        const int i = t >> 7;
+    const int lane = threadIdx.x & 31;
+    const bool active = lane >= C::HL && lane < 32 - C::HL;
+    const int xb = g.c0 + 4 * lane;
+    for (int i = threadIdx.x >> 5; i < C::WIN; i += PH_NW) {
         const int vy = vy0 + i;
-        const int gx = g.c0 + X;
-        double pxx = 0.0, pyy = 0.0, pxy = 0.0, pxt = 0.0, pyt = 0.0;
-        if ((unsigned)vy < (unsigned)H && (unsigned)gx < (unsigned)W) {
-            int s1 = sb + i + 1, s0 = sb + i;
-            if (s1 >= C::AB_ROWS) s1 -= C::AB_ROWS;
-            if (s0 >= C::AB_ROWS) s0 -= C::AB_ROWS;
-            // left neighbour: reflect-101 at the image border; strip column 0 has none (its
-            // products are never used: it only exists as the neighbour of column 1)
-            const int XL = gx == 0 ? (W > 1 ? X + 1 : X) : (X == 0 ? X : X - 1);
-            const double* up = s_ab + s0 * (2 * PH_PC);
-            const double* cr = s_ab + s1 * (2 * PH_PC);
-            const double a00 = up[XL], a01 = up[X], a10 = cr[XL], a11 = cr[X];
-            const double b00 = up[PH_PC + XL], b01 = up[PH_PC + X], b10 = cr[PH_PC + XL], b11 = cr[PH_PC + X];
+        double* d = s_prod + i * (5 * PH_PC) + 2 * lane;
+        if ((unsigned)vy >= (unsigned)H) {                   // warp-uniform
+            if (active) {
+                const double z[4] = {0.0, 0.0, 0.0, 0.0};
+#pragma unroll
+                for (int c = 0; c < 5; ++c) st4s(d + c * PH_PC, z);
+            }
+            continue;
+        }
+        int s1 = sb + i + 1, s0 = sb + i;
+        if (s1 >= C::AB_ROWS) s1 -= C::AB_ROWS;
+        if (s0 >= C::AB_ROWS) s0 -= C::AB_ROWS;
+        const double* up = s_ab + s0 * (2 * PH_PC) + 2 * lane;
+        const double* cr = s_ab + s1 * (2 * PH_PC) + 2 * lane;
+        double pA[4], pB[4], cA[4], cB[4];
+        ld4s(up, pA);
+        ld4s(up + PH_PC, pB);
+        ld4s(cr, cA);
+        ld4s(cr + PH_PC, cB);
+        // left neighbours (column xb - 1 = hi pair of lane - 1); lane 0 has none: its column 0
+        // only exists as the neighbour of column 1 and its products are never used
+        double pLA = up[64 - 1], pLB = up[PH_PC + 64 - 1], cLA = cr[64 - 1], cLB = cr[PH_PC + 64 - 1];
+        if (xb == 0) {                                       // reflect-101 at the left image border
+            pLA = pA[1]; pLB = pB[1]; cLA = cA[1]; cLB = cB[1];
+        }
+        double fx[4], fy[4], ft[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const double a00 = q ? pA[q - 1] : pLA, a01 = pA[q];
+            const double a10 = q ? cA[q - 1] : cLA, a11 = cA[q];
+            const double b00 = q ? pB[q - 1] : pLB, b01 = pB[q];
+            const double b10 = q ? cB[q - 1] : cLB, b11 = cB[q];
             const double fxa = dadd(dsub(dsub(a01, a00), a10), a11);
             const double fxb = dadd(dsub(dsub(b01, b00), b10), b11);
             const double sa = dadd(a00, a01), sbb = dadd(b00, b01);
@@ -193,72 +322,69 @@ __device__ __forceinline__ void phase_products(const PGeo& g, int vy0, int sb, c
             const double fyb = dadd(dsub(b10, sbb), b11);
             const double fta = -dadd(dadd(sa, a10), a11);
             const double ftb = dadd(dadd(sbb, b10), b11);
-            const double fx = dadd(fxa, fxb), fy = dadd(fya, fyb), ft = dadd(fta, ftb);
-            pxx = dmul(fx, fx);
-            pyy = dmul(fy, fy);
-            pxy = dmul(fx, fy);
-            pxt = dmul(fx, ft);
-            pyt = dmul(fy, ft);
+            fx[q] = dadd(fxa, fxb);
+            fy[q] = dadd(fya, fyb);
+            ft[q] = dadd(fta, ftb);
         }
-        double* d = s_prod + i * (5 * PH_PITCH) + ppos(X);
-        d[0] = pxx;
-        d[PH_PITCH] = pyy;
-        d[2 * PH_PITCH] = pxy;
-        d[3 * PH_PITCH] = pxt;
-        d[4 * PH_PITCH] = pyt;
+        if (g.edge) {                                        // columns outside the image contribute nothing
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const bool in = (unsigned)(xb + q) < (unsigned)W;
+                fx[q] = in ? fx[q] : 0.0;
+                fy[q] = in ? fy[q] : 0.0;
+                ft[q] = in ? ft[q] : 0.0;
+            }
+        }
+#pragma unroll
+        for (int c = 0; c < 5; ++c) {
+            double x[4], h[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+                x[q] = dmul(c == 1 || c == 4 ? fy[q] : fx[q], c == 0 ? fx[q] : (c == 1 || c == 2 ? fy[q] : ft[q]));
+            hsum4<R>(x, h);
+            if (active) st4s(d + c * PH_PC, h);
+        }
     }
 }
 
 // ------------------------------------------------------------------------------ P3
-// Vertical (2R+1)-row window sums of one (column, channel), in place.  van Herk / Gil-Werman:
-// the window of block row i is the suffix of the previous block from row i+1 plus the prefix
-// of this block up to row i.  ring[t] holds that suffix for row t+1 on entry and is refilled
-// with this block's raw rows, turned into suffix sums at the end -- all in registers.
+// Vertical (2R+1)-row window sums of one (channel, column pair), in place.  van Herk /
+// Gil-Werman: the window of block row i is the suffix of the previous block from row i+1 plus
+// the prefix of this block up to row i.  vs[t] holds that suffix for row t+1 on entry; this
+// block's raw rows stay in registers and are turned into the next suffix sums at the end.
 template <int R>
-__device__ __forceinline__ void phase_vertical(double* col, double (&ring)[2 * R])
+__device__ __forceinline__ void phase_vertical(double* col, double* vs)
 {
     constexpr int WIN = 2 * R + 1;
-    double P = 0.0;
+    double2 P = make_double2(0.0, 0.0);
+    double2 raw[2 * R];
 #pragma unroll
     for (int i = 0; i < WIN; ++i) {
-        const double p = col[i * (5 * PH_PITCH)];
-        P = i == 0 ? p : dadd(P, p);
-        double S = P;
-        if (i < WIN - 1) S = dadd(ring[i], P);
-        col[i * (5 * PH_PITCH)] = S;
-        if (i >= 1) ring[i - 1] = p;
-    }
-#pragma unroll
-    for (int t = 2 * R - 2; t >= 0; --t) ring[t] = dadd(ring[t], ring[t + 1]);
-}
-
-// ------------------------------------------------------------------------------ P4a
-// Horizontal (2R+1)-column window sums of the lines (row i, channel c) whose output row exists,
-// in place; one warp per line, lane = 4 consecutive columns.
-template <int R>
-__device__ __forceinline__ void phase_horizontal(double* s_prod, int i_lo, int i_hi)
-{
-    using C = PhaseCfg<R>;
-    const int lane = threadIdx.x & 31;
-    const int warp = threadIdx.x >> 5;
-    const bool active = lane >= C::HL && lane < 32 - C::HL;
-    for (int L = i_lo * 5 + warp; L < i_hi * 5; L += PH_NT / 32) {
-        double* row = s_prod + L * PH_PITCH + 2 * lane;
-        const double2 lo = *reinterpret_cast<const double2*>(row);
-        const double2 hi = *reinterpret_cast<const double2*>(row + 72);
-        const double x[4] = {lo.x, lo.y, hi.x, hi.y};
-        double h[4];
-        hsum4<R>(x, h);
-        if (active) {
-            *reinterpret_cast<double2*>(row) = make_double2(h[0], h[1]);
-            *reinterpret_cast<double2*>(row + 72) = make_double2(h[2], h[3]);
+        const double2 p = lds2(col + i * (5 * PH_PC));
+        if (i == 0) P = p;
+        else { P.x = dadd(P.x, p.x); P.y = dadd(P.y, p.y); }
+        double2 S = P;
+        if (i < WIN - 1) {
+            const double2 sf = lds2(vs + i * (5 * PH_PC));
+            S.x = dadd(sf.x, P.x);
+            S.y = dadd(sf.y, P.y);
         }
+        sts2(col + i * (5 * PH_PC), S.x, S.y);
+        if (i >= 1) raw[i - 1] = p;
+    }
+    double2 acc = raw[2 * R - 1];
+    sts2(vs + (2 * R - 1) * (5 * PH_PC), acc.x, acc.y);
+#pragma unroll
+    for (int t = 2 * R - 2; t >= 0; --t) {
+        acc.x = dadd(raw[t].x, acc.x);
+        acc.y = dadd(raw[t].y, acc.y);
+        sts2(vs + t * (5 * PH_PC), acc.x, acc.y);
     }
 }
 
-// ------------------------------------------------------------------------------ P4b
+// ------------------------------------------------------------------------------ P4
 // Guarded 2x2 solve (:407-542), += upsampled coarse flow (:634-637), stores, mask, gesture
-// statistics (:845-873) of output rows y0 + m, m = m0 + i, i = i_lo .. i_hi-1.
+// statistics (:845-873) of output rows y0 + m0 + i, i = i_lo .. i_hi-1; task = (row, 4 columns).
 struct StatAcc { unsigned long long x, y, c; };
 
 template <int R>
@@ -267,41 +393,90 @@ __device__ __forceinline__ void phase_solve(const LevelArgs& a, const PGeo& g, d
                                             int i_lo, int i_hi, const double* s_prod, StatAcc& st)
 {
     using C = PhaseCfg<R>;
+    constexpr int NPAIR = C::OUT_COLS / 2;                   // task = (row, pair of columns)
+    constexpr int HALF = (C::WIN + 1) / 2;                   // a thread takes rows ih and ih + HALF
+    if (threadIdx.x >= HALF * NPAIR) return;
     const int W = g.W, H = g.H;
     const double det_eps = a.det_eps, mag2 = a.mag2_thresh;
-    for (int t = threadIdx.x + i_lo * C::OUT_COLS; t < i_hi * C::OUT_COLS; t += PH_NT) {
-        const int i = t / C::OUT_COLS;
-        const int oc = t - i * C::OUT_COLS;
-        const int gx = g.xo0 + oc;
-        if (gx >= W) continue;
+    const int ih = threadIdx.x / NPAIR;
+    const int pr = threadIdx.x - ih * NPAIR;
+    const int xb = g.xo0 + 2 * pr;                           // even; W even: both columns exist or none
+    if (xb >= W) return;
+    const double* sp0 = s_prod + 2 * (C::HL + (pr >> 1)) + 64 * (pr & 1);
+#pragma unroll
+    for (int hh = 0; hh < 2; ++hh) {
+        const int i = ih + hh * HALF;
+        if (i < i_lo || i >= i_hi) continue;
         const int y = g.y0 + m0 + i;
-        const double* sp = s_prod + i * (5 * PH_PITCH) + ppos(4 * C::HL + oc);
-        const double sxx = sp[0], syy = sp[PH_PITCH], sxy = sp[2 * PH_PITCH];
-        const double sxt = sp[3 * PH_PITCH], syt = sp[4 * PH_PITCH];
-        const size_t o = (size_t)y * a.uv_pitch + gx;
-        double upu = 0.0, upv = 0.0;
-        if (g.has_coarse) { upu = U[o]; upv = V[o]; }
-        const bool interior = y >= R && y <= H - 1 - R && gx >= R && gx <= W - 1 - R;
-        const double det = dsub(dmul(sxx, syy), dmul(sxy, sxy));
-        const double nu = dsub(dmul(sxy, syt), dmul(syy, sxt));
-        const double nv = dsub(dmul(sxt, sxy), dmul(sxx, syt));
-        const bool ok = interior && fabs(det) > det_eps;
-        double lu, lv;
-        if (!div2_fast(nu, nv, det, lu, lv) && ok) {     // rare: exponent range outside the fast path
-            lu = ddiv_slow(nu, det);
-            lv = ddiv_slow(nv, det);
+        double* pu = U + (size_t)y * a.uv_pitch + xb;
+        double* pv = V + (size_t)y * a.uv_pitch + xb;
+        double upu[2] = {0.0, 0.0}, upv[2] = {0.0, 0.0};
+        if (g.has_coarse) {                                  // parked by P1 (same CTA, barriers between)
+            if (g.vec_uv) {
+                const double2 u0 = *reinterpret_cast<const double2*>(pu), v0 = *reinterpret_cast<const double2*>(pv);
+                upu[0] = u0.x; upu[1] = u0.y; upv[0] = v0.x; upv[1] = v0.y;
+            } else {
+                upu[0] = pu[0]; upu[1] = pu[1]; upv[0] = pv[0]; upv[1] = pv[1];
+            }
         }
-        lu = ok ? lu : 0.0;
-        lv = ok ? lv : 0.0;
-        const double fu = g.has_coarse ? dadd(lu, upu) : lu;
-        const double fv = g.has_coarse ? dadd(lv, upv) : lv;
-        U[o] = fu;
-        V[o] = fv;
-        if (M) M[(size_t)y * a.mask_pitch + gx] = ok ? 1 : 0;
+        const double* sp = sp0 + i * (5 * PH_PC);
+        const double2 sxx = lds2(sp), syy = lds2(sp + PH_PC), sxy = lds2(sp + 2 * PH_PC);
+        const double2 sxt = lds2(sp + 3 * PH_PC), syt = lds2(sp + 4 * PH_PC);
+        const bool yin = y >= R && y <= H - 1 - R;
+        double lu[2], lv[2], nus[2], nvs[2], dets[2];
+        unsigned okbits = 0;
+        bool fast = true;
+#pragma unroll
+        for (int q = 0; q < 2; ++q) {
+            const int x = xb + q;
+            const bool interior = yin && x >= R && x <= W - 1 - R;
+            const double xx = q ? sxx.y : sxx.x, yy = q ? syy.y : syy.x, xy = q ? sxy.y : sxy.x;
+            const double xt = q ? sxt.y : sxt.x, yt = q ? syt.y : syt.x;
+            dets[q] = dsub(dmul(xx, yy), dmul(xy, xy));
+            nus[q] = dsub(dmul(xy, yt), dmul(yy, xt));
+            nvs[q] = dsub(dmul(xt, xy), dmul(xx, yt));
+            const bool ok = interior && fabs(dets[q]) > det_eps;
+            okbits |= ok ? (1u << q) : 0u;
+            fast = (div2_fast(nus[q], nvs[q], dets[q], lu[q], lv[q]) || !ok) && fast;
+        }
+        if (!fast) {                                         // rare: exponent range outside the fast path
+#pragma unroll
+            for (int q = 0; q < 2; ++q) {
+                if ((okbits >> q) & 1u) {
+                    lu[q] = ddiv_slow(nus[q], dets[q]);
+                    lv[q] = ddiv_slow(nvs[q], dets[q]);
+                }
+            }
+        }
+        double fu[2], fv[2];
+#pragma unroll
+        for (int q = 0; q < 2; ++q) {
+            const bool ok = (okbits >> q) & 1u;
+            fu[q] = ok ? lu[q] : 0.0;
+            fv[q] = ok ? lv[q] : 0.0;
+            if (g.has_coarse) { fu[q] = dadd(fu[q], upu[q]); fv[q] = dadd(fv[q], upv[q]); }
+        }
+        if (g.vec_uv) {
+            *reinterpret_cast<double2*>(pu) = make_double2(fu[0], fu[1]);
+            *reinterpret_cast<double2*>(pv) = make_double2(fv[0], fv[1]);
+        } else {
+            pu[0] = fu[0]; pu[1] = fu[1]; pv[0] = fv[0]; pv[1] = fv[1];
+        }
+        if (M) {
+            unsigned char* pm = M + (size_t)y * a.mask_pitch + xb;
+            pm[0] = (unsigned char)(okbits & 1u);
+            pm[1] = (unsigned char)((okbits >> 1) & 1u);
+        }
         if (a.stats) {
-            // val = sqrt(u^2 + v^2); !(val < mag_thresh)  <=>  !(u^2 + v^2 < mag2)
-            const double s2 = dadd(dmul(fu, fu), dmul(fv, fv));
-            if (!(s2 < mag2)) { st.x += (unsigned)gx; st.y += (unsigned)y; st.c += 1; }
+            unsigned rc = 0;
+#pragma unroll
+            for (int q = 0; q < 2; ++q) {
+                // val = sqrt(u^2 + v^2); !(val < mag_thresh)  <=>  !(u^2 + v^2 < mag2)
+                const double s2 = dadd(dmul(fu[q], fu[q]), dmul(fv[q], fv[q]));
+                if (!(s2 < mag2)) { st.x += (unsigned)(xb + q); rc += 1u; }
+            }
+            st.c += rc;
+            st.y += (unsigned long long)rc * (unsigned)y;
         }
     }
 }
@@ -315,6 +490,7 @@ __global__ void __launch_bounds__(PH_NT, 1) lk_level_phase_kernel(LevelArgs a, i
     double* s_prod = sm;
     double* s_ab = s_prod + C::PROD_D;
     double* s_hr = s_ab + C::AB_D;
+    double* s_vs = s_hr + C::HR_D;
 
     PGeo g;
     g.W = a.w;
@@ -324,6 +500,7 @@ __global__ void __launch_bounds__(PH_NT, 1) lk_level_phase_kernel(LevelArgs a, i
     g.y0 = blockIdx.y * th;
     g.y1 = min(g.y0 + th, a.h);
     g.has_coarse = a.cu != nullptr;
+    g.edge = g.c0 < 0 || g.c0 + PH_PC > a.w;
     const int pair = blockIdx.z;
     const int H = g.H;
 
@@ -334,45 +511,78 @@ __global__ void __launch_bounds__(PH_NT, 1) lk_level_phase_kernel(LevelArgs a, i
     double* U = a.u + (size_t)pair * a.uv_pair_stride;
     double* V = a.v + (size_t)pair * a.uv_pair_stride;
     unsigned char* M = a.mask ? a.mask + (size_t)pair * a.mask_pair_stride : nullptr;
+    g.vec_img = ((reinterpret_cast<uintptr_t>(A) | reinterpret_cast<uintptr_t>(B) | (a.img_pitch * 8)) & 15) == 0;
+    g.vec_uv = ((reinterpret_cast<uintptr_t>(U) | reinterpret_cast<uintptr_t>(V) | (a.uv_pitch * 8)) & 15) == 0;
+    g.vec_c = false;
 
-    // P3 ownership: thread -> (channel, strip column)
-    double* vcol = s_prod + (threadIdx.x >> 7) * PH_PITCH + ppos(threadIdx.x & (PH_PC - 1));
-    double ring[2 * R];
-#pragma unroll
-    for (int t = 0; t < 2 * R; ++t) ring[t] = 0.0;
+    // P3 ownership: thread -> (channel, pair of output columns)
+    const bool v_task = threadIdx.x < 5 * C::VPAIRS;
+    int voff;
+    {
+        const int ch = threadIdx.x / C::VPAIRS, q = threadIdx.x - ch * C::VPAIRS;
+        const int half = q / C::OUT_LANES, ol = q - half * C::OUT_LANES;
+        voff = v_task ? ch * PH_PC + half * 64 + 2 * (C::HL + ol) : 0;
+    }
+    for (int t = threadIdx.x; t < C::VS_D; t += PH_NT) s_vs[t] = 0.0;
+    __syncthreads();
     StatAcc st = {0, 0, 0};
 
     const int rows = g.y1 - g.y0;
     const int n_steps = (rows + 2 * R + C::WIN - 1) / C::WIN;
-    int sb = 0;                                        // (s * WIN) mod AB_ROWS
-    for (int s = 0; s < n_steps; ++s) {
-        const int vy0 = g.y0 - R + s * C::WIN;         // product row of block row 0
-        const int r_lo = s == 0 ? 0 : 1;
-        // fine rows this step warps: [vlo, vhi]; source rows after border handling: [lo, hi]
-        const int vlo = vy0 + r_lo - 1, vhi = vy0 + C::WIN - 1;
+    const int warp = threadIdx.x >> 5;
+
+    // Step s warps fine rows vy0 + r - 1, r = r_lo .. WIN, and needs the coarse rows ka .. ka+nk-1.
+    struct Step { int vy0, r_lo, sb, ka, nk; bool any; };
+    auto step_geo = [&](int s) {
+        Step q;
+        q.vy0 = g.y0 - R + s * C::WIN;                 // product row of block row 0
+        q.r_lo = s == 0 ? 0 : 1;
+        q.sb = (s * C::WIN) % C::AB_ROWS;
+        // rows [vlo, vhi]; source rows after border handling: [lo, hi]
+        const int vlo = q.vy0 + q.r_lo - 1, vhi = q.vy0 + C::WIN - 1;
         int lo = max(vlo, 0), hi = min(vhi, H - 1);
         if (vlo <= -1 && vhi >= -1) { lo = 0; hi = max(hi, min(1, H - 1)); }
-        const int ka = (lo >> 1) - 1;
-        if (lo <= hi) {
-            if (g.has_coarse) {
-                phase_up_rows(a, g, cu, cv, ka, (hi >> 1) + 1 - ka + 1, s_hr);
-                __syncthreads();
-            }
-            phase_remap<R>(a, g, A, B, U, V, vy0, r_lo, sb, ka, s_hr, s_ab);
+        q.ka = (lo >> 1) - 1;
+        q.nk = (hi >> 1) + 2 - q.ka;
+        q.any = lo <= hi && s < n_steps;
+        return q;
+    };
+
+    // Schedule: three block-wide phases per step, arranged so that the latency-bound work of the
+    // next step (coarse-flow rows, gathers) runs next to compute-bound work of the current one:
+    //   beta  : P2(s), with the loads of P0(s+1) in flight meanwhile
+    //   gamma : P3(s)
+    //   alpha : P4(s) and P1(s+1); odd warps do P4 first, even warps P1 first
+    Step cur = step_geo(0);
+    if (cur.any) {
+        if (g.has_coarse) {
+            UpPre q;
+            up_rows_issue<C::HR_ROWS>(a, g, cu, cv, cur.ka, cur.nk, q);
+            up_rows_finish(a, g, cu, cv, cur.ka, cur.nk, q, s_hr);
+            __syncthreads();
+        }
+        phase_remap<R>(a, g, A, B, U, V, cur.vy0, cur.r_lo, cur.sb, cur.ka, s_hr, s_ab);
+    }
+    __syncthreads();
+    for (int s = 0; s < n_steps; ++s) {
+        const Step nxt = step_geo(s + 1);
+        {
+            UpPre q;
+            const bool up = nxt.any && g.has_coarse;
+            if (up) up_rows_issue<C::HR_ROWS>(a, g, cu, cv, nxt.ka, nxt.nk, q);
+            phase_products<R>(g, cur.vy0, cur.sb, s_ab, s_prod);
+            if (up) up_rows_finish(a, g, cu, cv, nxt.ka, nxt.nk, q, s_hr);
         }
         __syncthreads();
-        phase_products<R>(g, vy0, sb, s_ab, s_prod);
-        __syncthreads();
-        phase_vertical<R>(vcol, ring);
+        if (v_task) phase_vertical<R>(s_prod + voff, s_vs + voff);
         __syncthreads();
         const int m0 = C::WIN * (s - 1) + 1;           // output row (relative to y0) of block row 0
         const int i_lo = max(0, -m0), i_hi = min(C::WIN, rows - m0);
-        phase_horizontal<R>(s_prod, i_lo, i_hi);
+        if (warp & 1) phase_solve<R>(a, g, U, V, M, m0, i_lo, i_hi, s_prod, st);
+        if (nxt.any) phase_remap<R>(a, g, A, B, U, V, nxt.vy0, nxt.r_lo, nxt.sb, nxt.ka, s_hr, s_ab);
+        if (!(warp & 1)) phase_solve<R>(a, g, U, V, M, m0, i_lo, i_hi, s_prod, st);
         __syncthreads();
-        phase_solve<R>(a, g, U, V, M, m0, i_lo, i_hi, s_prod, st);
-        __syncthreads();
-        sb += C::WIN;
-        if (sb >= C::AB_ROWS) sb -= C::AB_ROWS;
+        cur = nxt;
     }
 
     if (a.stats) {
