@@ -40,6 +40,8 @@ namespace {
 constexpr int PH_NT = 512;       // threads per CTA (16 warps; a warp = one row of 32 quads)
 constexpr int PH_NW = PH_NT / 32;
 constexpr int PH_PC = 128;       // product columns per strip = 32 lanes x 4 columns
+constexpr int AB_HALF = 72;      // warped-frame rows: lo pairs [0,64), hi pairs [72,136)
+constexpr int AB_PITCH = 136;
 
 template <int R>
 struct PhaseCfg {
@@ -50,27 +52,32 @@ struct PhaseCfg {
     static constexpr int WIN = 2 * R + 1;             // rows per step = vertical block length
     static constexpr int AB_ROWS = WIN + 1;           // + the row above the step
     static constexpr int HR_ROWS = (WIN + 1) / 2 + 3; // coarse rows a step can touch
-    static constexpr int PROD_D = WIN * 5 * PH_PC;
-    static constexpr int AB_D = AB_ROWS * 2 * PH_PC;
+    // window-sum rows hold the OUT_COLS output columns, pair-split: lo pairs, then hi pairs at PHALF
+    static constexpr int PHALF = (2 * OUT_LANES + 7) / 16 * 16 + 8;
+    static constexpr int PPITCH = PHALF + 2 * OUT_LANES;
+    static constexpr int PROD_D = WIN * 5 * PPITCH;
+    static constexpr int AB_D = AB_ROWS * 2 * AB_PITCH;
     static constexpr int HR_D = HR_ROWS * 2 * PH_PC;
-    static constexpr int VS_D = 2 * R * 5 * PH_PC;    // suffix sums of the previous vertical block
+    static constexpr int VS_D = 2 * R * 5 * PPITCH;   // suffix sums of the previous vertical block
     static constexpr size_t SMEM_BYTES = (size_t)(PROD_D + AB_D + HR_D + VS_D) * 8;
     static constexpr int VPAIRS = 2 * OUT_LANES;      // column pairs per channel in P3
 };
 
-// All shared-memory rows are "pair-split": columns 4j, 4j+1 of lane j sit at lo[2j], columns
-// 4j+2, 4j+3 at hi[2j] = row[64 + 2j], so that every 128-bit access of a warp is contiguous.
+// Shared-memory rows that are read four columns per lane are "pair-split": columns 4j, 4j+1 of
+// lane j sit at lo[2j], columns 4j+2, 4j+3 at hi[2j] = row[half + 2j], so that every 128-bit
+// access of a warp is contiguous.  half = 8 (mod 16) doubles makes the column-per-lane and
+// pair-per-lane accesses of the other phases conflict-free as well.
 __device__ __forceinline__ double2 lds2(const double* p) { return *reinterpret_cast<const double2*>(p); }
 __device__ __forceinline__ void sts2(double* p, double x, double y) { *reinterpret_cast<double2*>(p) = make_double2(x, y); }
-__device__ __forceinline__ void ld4s(const double* p, double (&v)[4])
+__device__ __forceinline__ void ld4s(const double* p, int half, double (&v)[4])
 {
-    const double2 a = lds2(p), b = lds2(p + 64);
+    const double2 a = lds2(p), b = lds2(p + half);
     v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y;
 }
-__device__ __forceinline__ void st4s(double* p, const double (&v)[4])
+__device__ __forceinline__ void st4s(double* p, int half, const double (&v)[4])
 {
     sts2(p, v[0], v[1]);
-    sts2(p + 64, v[2], v[3]);
+    sts2(p + half, v[2], v[3]);
 }
 
 struct PGeo {
@@ -83,8 +90,8 @@ struct PGeo {
     bool vec_img, vec_uv, vec_c;   // 16-byte alignment of the image / flow / coarse-flow rows
 };
 
-// Position of strip column X inside a pair-split row.
-__device__ __forceinline__ int ppos(int X) { return ((X & 2) << 5) + 2 * (X >> 2) + (X & 1); }
+// Position of strip column X inside a warped-frame row.
+__device__ __forceinline__ int ppos(int X) { return ((X & 2) ? AB_HALF : 0) + 2 * (X >> 2) + (X & 1); }
 
 // ------------------------------------------------------------------------------ P0
 // Horizontal pass of cv::pyrUp (:646-647) of coarse rows rho(ka) .. rho(ka + nk - 1), both
@@ -147,27 +154,28 @@ __device__ __forceinline__ void up_rows_finish(const LevelArgs& a, const PGeo& g
 
 // ------------------------------------------------------------------------------ P1
 // Warped frames A', B' (:667-700) of fine rows vy0 + r - 1, r = r_lo .. WIN, into the AB block
-// (slot of r = (sb + r) mod AB_ROWS); one warp per row, a lane takes the columns lane + 32 i so
+// (slot of r = (sb + r) mod AB_ROWS); the calling warp takes the rows r_first, r_first + r_step,
+// ...; one warp per row, a lane takes the columns lane + 32 i so
 // that every gather instruction of the warp reads 32 neighbouring pixels.  Row -1 is the
 // reflect-101 row above row 0 (image row 1); other rows outside the image are never read.
 template <int R>
 __device__ __forceinline__ void phase_remap(const LevelArgs& a, const PGeo& g, const double* __restrict__ A,
                                             const double* __restrict__ B, double* __restrict__ U,
-                                            double* __restrict__ V, int vy0, int r_lo, int sb, int ka,
-                                            const double* s_hr, double* s_ab)
+                                            double* __restrict__ V, int vy0, int r_first, int r_step, int sb,
+                                            int ka, const double* s_hr, double* s_ab)
 {
     using C = PhaseCfg<R>;
     const int W = g.W, H = g.H;
     const int pitch = (int)a.img_pitch;
     const int lane = threadIdx.x & 31;
-    for (int r = (threadIdx.x >> 5) + r_lo; r <= C::WIN; r += PH_NW) {
+    for (int r = r_first; r <= C::WIN; r += r_step) {
         const int vy = vy0 + r - 1;
         int yy = vy;
         if (vy == -1) yy = H > 1 ? 1 : 0;
         else if ((unsigned)vy >= (unsigned)H) continue;
         int slot = sb + r;
         if (slot >= C::AB_ROWS) slot -= C::AB_ROWS;
-        double* dst = s_ab + slot * (2 * PH_PC);
+        double* dst = s_ab + slot * (2 * AB_PITCH);
         double va[4] = {0.0, 0.0, 0.0, 0.0}, vb[4] = {0.0, 0.0, 0.0, 0.0};
         const int x0 = g.c0 + lane;
         unsigned inm = 0;                                    // columns of this lane inside the image
@@ -263,7 +271,7 @@ __device__ __forceinline__ void phase_remap(const LevelArgs& a, const PGeo& g, c
             const bool in = (inm >> i) & 1u;
             const int q = ppos(lane + 32 * i);
             dst[q] = in ? va[i] : 0.0;
-            dst[PH_PC + q] = in ? vb[i] : 0.0;
+            dst[AB_PITCH + q] = in ? vb[i] : 0.0;
         }
     }
 }
@@ -283,28 +291,29 @@ __device__ __forceinline__ void phase_products(const PGeo& g, int vy0, int sb, c
     const int xb = g.c0 + 4 * lane;
     for (int i = threadIdx.x >> 5; i < C::WIN; i += PH_NW) {
         const int vy = vy0 + i;
-        double* d = s_prod + i * (5 * PH_PC) + 2 * lane;
+        double* d = s_prod + i * (5 * C::PPITCH) + 2 * (lane - C::HL);
         if ((unsigned)vy >= (unsigned)H) {                   // warp-uniform
             if (active) {
                 const double z[4] = {0.0, 0.0, 0.0, 0.0};
 #pragma unroll
-                for (int c = 0; c < 5; ++c) st4s(d + c * PH_PC, z);
+                for (int c = 0; c < 5; ++c) st4s(d + c * C::PPITCH, C::PHALF, z);
             }
             continue;
         }
         int s1 = sb + i + 1, s0 = sb + i;
         if (s1 >= C::AB_ROWS) s1 -= C::AB_ROWS;
         if (s0 >= C::AB_ROWS) s0 -= C::AB_ROWS;
-        const double* up = s_ab + s0 * (2 * PH_PC) + 2 * lane;
-        const double* cr = s_ab + s1 * (2 * PH_PC) + 2 * lane;
+        const double* up = s_ab + s0 * (2 * AB_PITCH) + 2 * lane;
+        const double* cr = s_ab + s1 * (2 * AB_PITCH) + 2 * lane;
         double pA[4], pB[4], cA[4], cB[4];
-        ld4s(up, pA);
-        ld4s(up + PH_PC, pB);
-        ld4s(cr, cA);
-        ld4s(cr + PH_PC, cB);
+        ld4s(up, AB_HALF, pA);
+        ld4s(up + AB_PITCH, AB_HALF, pB);
+        ld4s(cr, AB_HALF, cA);
+        ld4s(cr + AB_PITCH, AB_HALF, cB);
         // left neighbours (column xb - 1 = hi pair of lane - 1); lane 0 has none: its column 0
         // only exists as the neighbour of column 1 and its products are never used
-        double pLA = up[64 - 1], pLB = up[PH_PC + 64 - 1], cLA = cr[64 - 1], cLB = cr[PH_PC + 64 - 1];
+        double pLA = up[AB_HALF - 1], pLB = up[AB_PITCH + AB_HALF - 1];
+        double cLA = cr[AB_HALF - 1], cLB = cr[AB_PITCH + AB_HALF - 1];
         if (xb == 0) {                                       // reflect-101 at the left image border
             pLA = pA[1]; pLB = pB[1]; cLA = cA[1]; cLB = cB[1];
         }
@@ -342,7 +351,7 @@ __device__ __forceinline__ void phase_products(const PGeo& g, int vy0, int sb, c
             for (int q = 0; q < 4; ++q)
                 x[q] = dmul(c == 1 || c == 4 ? fy[q] : fx[q], c == 0 ? fx[q] : (c == 1 || c == 2 ? fy[q] : ft[q]));
             hsum4<R>(x, h);
-            if (active) st4s(d + c * PH_PC, h);
+            if (active) st4s(d + c * C::PPITCH, C::PHALF, h);
         }
     }
 }
@@ -356,57 +365,54 @@ template <int R>
 __device__ __forceinline__ void phase_vertical(double* col, double* vs)
 {
     constexpr int WIN = 2 * R + 1;
+    constexpr int ROW = 5 * PhaseCfg<R>::PPITCH;
     double2 P = make_double2(0.0, 0.0);
     double2 raw[2 * R];
 #pragma unroll
     for (int i = 0; i < WIN; ++i) {
-        const double2 p = lds2(col + i * (5 * PH_PC));
+        const double2 p = lds2(col + i * ROW);
         if (i == 0) P = p;
         else { P.x = dadd(P.x, p.x); P.y = dadd(P.y, p.y); }
         double2 S = P;
         if (i < WIN - 1) {
-            const double2 sf = lds2(vs + i * (5 * PH_PC));
+            const double2 sf = lds2(vs + i * ROW);
             S.x = dadd(sf.x, P.x);
             S.y = dadd(sf.y, P.y);
         }
-        sts2(col + i * (5 * PH_PC), S.x, S.y);
+        sts2(col + i * ROW, S.x, S.y);
         if (i >= 1) raw[i - 1] = p;
     }
     double2 acc = raw[2 * R - 1];
-    sts2(vs + (2 * R - 1) * (5 * PH_PC), acc.x, acc.y);
+    sts2(vs + (2 * R - 1) * ROW, acc.x, acc.y);
 #pragma unroll
     for (int t = 2 * R - 2; t >= 0; --t) {
         acc.x = dadd(raw[t].x, acc.x);
         acc.y = dadd(raw[t].y, acc.y);
-        sts2(vs + t * (5 * PH_PC), acc.x, acc.y);
+        sts2(vs + t * ROW, acc.x, acc.y);
     }
 }
 
 // ------------------------------------------------------------------------------ P4
 // Guarded 2x2 solve (:407-542), += upsampled coarse flow (:634-637), stores, mask, gesture
-// statistics (:845-873) of output rows y0 + m0 + i, i = i_lo .. i_hi-1; task = (row, 4 columns).
+// statistics (:845-873) of output rows y0 + m0 + i, i = i_lo .. i_hi-1, by the threads tid0 of nthr.
 struct StatAcc { unsigned long long x, y, c; };
 
 template <int R>
 __device__ __forceinline__ void phase_solve(const LevelArgs& a, const PGeo& g, double* __restrict__ U,
                                             double* __restrict__ V, unsigned char* __restrict__ M, int m0,
-                                            int i_lo, int i_hi, const double* s_prod, StatAcc& st)
+                                            int i_lo, int i_hi, const double* s_prod, StatAcc& st, int tid0, int nthr)
 {
     using C = PhaseCfg<R>;
     constexpr int NPAIR = C::OUT_COLS / 2;                   // task = (row, pair of columns)
-    constexpr int HALF = (C::WIN + 1) / 2;                   // a thread takes rows ih and ih + HALF
-    if (threadIdx.x >= HALF * NPAIR) return;
     const int W = g.W, H = g.H;
     const double det_eps = a.det_eps, mag2 = a.mag2_thresh;
-    const int ih = threadIdx.x / NPAIR;
-    const int pr = threadIdx.x - ih * NPAIR;
-    const int xb = g.xo0 + 2 * pr;                           // even; W even: both columns exist or none
-    if (xb >= W) return;
-    const double* sp0 = s_prod + 2 * (C::HL + (pr >> 1)) + 64 * (pr & 1);
-#pragma unroll
-    for (int hh = 0; hh < 2; ++hh) {
-        const int i = ih + hh * HALF;
-        if (i < i_lo || i >= i_hi) continue;
+    for (int t = tid0; t < (i_hi - i_lo) * NPAIR; t += nthr) {
+        const int ir = t / NPAIR;
+        const int pr = t - ir * NPAIR;
+        const int i = i_lo + ir;
+        const int xb = g.xo0 + 2 * pr;                       // even; W even: both columns exist or none
+        if (xb >= W) continue;
+        const double* sp0 = s_prod + 2 * (pr >> 1) + C::PHALF * (pr & 1);
         const int y = g.y0 + m0 + i;
         double* pu = U + (size_t)y * a.uv_pitch + xb;
         double* pv = V + (size_t)y * a.uv_pitch + xb;
@@ -419,9 +425,9 @@ __device__ __forceinline__ void phase_solve(const LevelArgs& a, const PGeo& g, d
                 upu[0] = pu[0]; upu[1] = pu[1]; upv[0] = pv[0]; upv[1] = pv[1];
             }
         }
-        const double* sp = sp0 + i * (5 * PH_PC);
-        const double2 sxx = lds2(sp), syy = lds2(sp + PH_PC), sxy = lds2(sp + 2 * PH_PC);
-        const double2 sxt = lds2(sp + 3 * PH_PC), syt = lds2(sp + 4 * PH_PC);
+        const double* sp = sp0 + i * (5 * C::PPITCH);
+        const double2 sxx = lds2(sp), syy = lds2(sp + C::PPITCH), sxy = lds2(sp + 2 * C::PPITCH);
+        const double2 sxt = lds2(sp + 3 * C::PPITCH), syt = lds2(sp + 4 * C::PPITCH);
         const bool yin = y >= R && y <= H - 1 - R;
         double lu[2], lv[2], nus[2], nvs[2], dets[2];
         unsigned okbits = 0;
@@ -521,7 +527,7 @@ __global__ void __launch_bounds__(PH_NT, 1) lk_level_phase_kernel(LevelArgs a, i
     {
         const int ch = threadIdx.x / C::VPAIRS, q = threadIdx.x - ch * C::VPAIRS;
         const int half = q / C::OUT_LANES, ol = q - half * C::OUT_LANES;
-        voff = v_task ? ch * PH_PC + half * 64 + 2 * (C::HL + ol) : 0;
+        voff = v_task ? ch * C::PPITCH + half * C::PHALF + 2 * ol : 0;
     }
     for (int t = threadIdx.x; t < C::VS_D; t += PH_NT) s_vs[t] = 0.0;
     __syncthreads();
@@ -548,11 +554,17 @@ __global__ void __launch_bounds__(PH_NT, 1) lk_level_phase_kernel(LevelArgs a, i
         return q;
     };
 
-    // Schedule: three block-wide phases per step, arranged so that the latency-bound work of the
-    // next step (coarse-flow rows, gathers) runs next to compute-bound work of the current one:
-    //   beta  : P2(s), with the loads of P0(s+1) in flight meanwhile
-    //   gamma : P3(s)
-    //   alpha : P4(s) and P1(s+1); odd warps do P4 first, even warps P1 first
+    // Schedule of a step (two block-wide barriers):
+    //   beta : P2(s), with the loads of P0(s+1) in flight meanwhile
+    //   gamma: the first V_WARPS warps ("V") run P3(s), signal barrier 1 and go on to rows of
+    //          P1(s+1); the other warps ("O") start with rows of P1(s+1), wait for barrier 1 and
+    //          run P4(s).  The latency-bound gathers thus overlap the shared-memory-bound
+    //          vertical sums and the arithmetic of the solve.
+    constexpr int V_WARPS = (5 * C::VPAIRS + 31) / 32;
+    constexpr int O_WARPS = PH_NW - V_WARPS;
+    const int my_row = warp >= V_WARPS ? C::WIN - (warp - V_WARPS)
+                                       : (1 + warp <= C::WIN - O_WARPS ? 1 + warp : C::WIN + 1);
+    static_assert(C::WIN - O_WARPS <= V_WARPS, "not enough warps for the rows of P1");
     Step cur = step_geo(0);
     if (cur.any) {
         if (g.has_coarse) {
@@ -561,7 +573,7 @@ __global__ void __launch_bounds__(PH_NT, 1) lk_level_phase_kernel(LevelArgs a, i
             up_rows_finish(a, g, cu, cv, cur.ka, cur.nk, q, s_hr);
             __syncthreads();
         }
-        phase_remap<R>(a, g, A, B, U, V, cur.vy0, cur.r_lo, cur.sb, cur.ka, s_hr, s_ab);
+        phase_remap<R>(a, g, A, B, U, V, cur.vy0, warp + cur.r_lo, PH_NW, cur.sb, cur.ka, s_hr, s_ab);
     }
     __syncthreads();
     for (int s = 0; s < n_steps; ++s) {
@@ -574,13 +586,18 @@ __global__ void __launch_bounds__(PH_NT, 1) lk_level_phase_kernel(LevelArgs a, i
             if (up) up_rows_finish(a, g, cu, cv, nxt.ka, nxt.nk, q, s_hr);
         }
         __syncthreads();
-        if (v_task) phase_vertical<R>(s_prod + voff, s_vs + voff);
-        __syncthreads();
         const int m0 = C::WIN * (s - 1) + 1;           // output row (relative to y0) of block row 0
         const int i_lo = max(0, -m0), i_hi = min(C::WIN, rows - m0);
-        if (warp & 1) phase_solve<R>(a, g, U, V, M, m0, i_lo, i_hi, s_prod, st);
-        if (nxt.any) phase_remap<R>(a, g, A, B, U, V, nxt.vy0, nxt.r_lo, nxt.sb, nxt.ka, s_hr, s_ab);
-        if (!(warp & 1)) phase_solve<R>(a, g, U, V, M, m0, i_lo, i_hi, s_prod, st);
+        const int r_mine = nxt.any && my_row >= 1 ? my_row : C::WIN + 1;
+        if (warp < V_WARPS) {
+            if (v_task) phase_vertical<R>(s_prod + voff, s_vs + voff);
+            asm volatile("bar.arrive 1, %0;" ::"n"(PH_NT) : "memory");
+            phase_remap<R>(a, g, A, B, U, V, nxt.vy0, r_mine, C::WIN + 1, nxt.sb, nxt.ka, s_hr, s_ab);
+        } else {
+            phase_remap<R>(a, g, A, B, U, V, nxt.vy0, r_mine, C::WIN + 1, nxt.sb, nxt.ka, s_hr, s_ab);
+            asm volatile("bar.sync 1, %0;" ::"n"(PH_NT) : "memory");
+            phase_solve<R>(a, g, U, V, M, m0, i_lo, i_hi, s_prod, st, threadIdx.x - V_WARPS * 32, O_WARPS * 32);
+        }
         __syncthreads();
         cur = nxt;
     }
