@@ -37,6 +37,10 @@ namespace ofb {
 
 namespace {
 
+#ifndef PH_CUT_A
+#define PH_CUT_A 32              // share (in 1/32) of the P4 tasks taken by the O warps ...
+#define PH_CUT_B 32              // ... and up to which the last V warp takes them
+#endif
 constexpr int PH_NT = 512;       // threads per CTA (16 warps; a warp = one row of 32 quads)
 constexpr int PH_NW = PH_NT / 32;
 constexpr int PH_PC = 128;       // product columns per strip = 32 lanes x 4 columns
@@ -394,19 +398,21 @@ __device__ __forceinline__ void phase_vertical(double* col, double* vs)
 
 // ------------------------------------------------------------------------------ P4
 // Guarded 2x2 solve (:407-542), += upsampled coarse flow (:634-637), stores, mask, gesture
-// statistics (:845-873) of output rows y0 + m0 + i, i = i_lo .. i_hi-1, by the threads tid0 of nthr.
+// statistics (:845-873) of output rows y0 + m0 + i, i = i_lo .. i_hi-1; tasks (row, column pair)
+// t_begin, t_begin + nthr, ... < t_end of the (i_hi - i_lo) * OUT_COLS / 2 tasks.
 struct StatAcc { unsigned long long x, y, c; };
 
 template <int R>
 __device__ __forceinline__ void phase_solve(const LevelArgs& a, const PGeo& g, double* __restrict__ U,
                                             double* __restrict__ V, unsigned char* __restrict__ M, int m0,
-                                            int i_lo, int i_hi, const double* s_prod, StatAcc& st, int tid0, int nthr)
+                                            int i_lo, int i_hi, const double* s_prod, StatAcc& st, int t_begin,
+                                            int t_end, int nthr)
 {
     using C = PhaseCfg<R>;
     constexpr int NPAIR = C::OUT_COLS / 2;                   // task = (row, pair of columns)
     const int W = g.W, H = g.H;
     const double det_eps = a.det_eps, mag2 = a.mag2_thresh;
-    for (int t = tid0; t < (i_hi - i_lo) * NPAIR; t += nthr) {
+    for (int t = t_begin; t < t_end; t += nthr) {
         const int ir = t / NPAIR;
         const int pr = t - ir * NPAIR;
         const int i = i_lo + ir;
@@ -556,47 +562,57 @@ __global__ void __launch_bounds__(PH_NT, 1) lk_level_phase_kernel(LevelArgs a, i
 
     // Schedule of a step (two block-wide barriers):
     //   beta : P2(s), with the loads of P0(s+1) in flight meanwhile
-    //   gamma: the first V_WARPS warps ("V") run P3(s), signal barrier 1 and go on to rows of
-    //          P1(s+1); the other warps ("O") start with rows of P1(s+1), wait for barrier 1 and
-    //          run P4(s).  The latency-bound gathers thus overlap the shared-memory-bound
-    //          vertical sums and the arithmetic of the solve.
+    //   gamma: the first V_WARPS warps ("V") run P3(s) and signal barrier 1; every warp then warps
+    //          its row of P1(s+1); finally P4(s), for which the other warps ("O") wait on barrier 1.
+    //          The latency-bound gathers thus overlap the shared-memory-bound vertical sums and
+    //          the arithmetic of the solve.
+    // The loop starts at s = -1 (only P0(0), P1(0)) so that every phase has a single call site:
+    // the code of a step has to stay small enough for the instruction cache.
     constexpr int V_WARPS = (5 * C::VPAIRS + 31) / 32;
     constexpr int O_WARPS = PH_NW - V_WARPS;
+    static_assert(C::WIN - O_WARPS < V_WARPS, "not enough warps for the rows of P1");
+    // rows of P1: O warps take WIN, WIN-1, ...; V warps 1, 2, ...; the last V warp has no row in
+    // steady state and takes row 0, which only exists in the first step
     const int my_row = warp >= V_WARPS ? C::WIN - (warp - V_WARPS)
-                                       : (1 + warp <= C::WIN - O_WARPS ? 1 + warp : C::WIN + 1);
-    static_assert(C::WIN - O_WARPS <= V_WARPS, "not enough warps for the rows of P1");
+                                       : (1 + warp <= C::WIN - O_WARPS ? 1 + warp : (warp == V_WARPS - 1 ? 0 : -1));
     Step cur = step_geo(0);
-    if (cur.any) {
-        if (g.has_coarse) {
-            UpPre q;
-            up_rows_issue<C::HR_ROWS>(a, g, cu, cv, cur.ka, cur.nk, q);
-            up_rows_finish(a, g, cu, cv, cur.ka, cur.nk, q, s_hr);
-            __syncthreads();
-        }
-        phase_remap<R>(a, g, A, B, U, V, cur.vy0, warp + cur.r_lo, PH_NW, cur.sb, cur.ka, s_hr, s_ab);
-    }
-    __syncthreads();
-    for (int s = 0; s < n_steps; ++s) {
+    cur.any = false;
+    for (int s = -1; s < n_steps; ++s) {
         const Step nxt = step_geo(s + 1);
         {
             UpPre q;
             const bool up = nxt.any && g.has_coarse;
             if (up) up_rows_issue<C::HR_ROWS>(a, g, cu, cv, nxt.ka, nxt.nk, q);
-            phase_products<R>(g, cur.vy0, cur.sb, s_ab, s_prod);
+            if (s >= 0) phase_products<R>(g, cur.vy0, cur.sb, s_ab, s_prod);
             if (up) up_rows_finish(a, g, cu, cv, nxt.ka, nxt.nk, q, s_hr);
         }
         __syncthreads();
         const int m0 = C::WIN * (s - 1) + 1;           // output row (relative to y0) of block row 0
-        const int i_lo = max(0, -m0), i_hi = min(C::WIN, rows - m0);
-        const int r_mine = nxt.any && my_row >= 1 ? my_row : C::WIN + 1;
-        if (warp < V_WARPS) {
+        const int i_lo = max(0, -m0), i_hi = s >= 0 ? min(C::WIN, rows - m0) : 0;
+        if (warp < V_WARPS && s >= 0) {
             if (v_task) phase_vertical<R>(s_prod + voff, s_vs + voff);
             asm volatile("bar.arrive 1, %0;" ::"n"(PH_NT) : "memory");
+        }
+        {
+            const int r_mine = nxt.any && my_row >= nxt.r_lo ? my_row : C::WIN + 1;
             phase_remap<R>(a, g, A, B, U, V, nxt.vy0, r_mine, C::WIN + 1, nxt.sb, nxt.ka, s_hr, s_ab);
-        } else {
-            phase_remap<R>(a, g, A, B, U, V, nxt.vy0, r_mine, C::WIN + 1, nxt.sb, nxt.ka, s_hr, s_ab);
-            asm volatile("bar.sync 1, %0;" ::"n"(PH_NT) : "memory");
-            phase_solve<R>(a, g, U, V, M, m0, i_lo, i_hi, s_prod, st, threadIdx.x - V_WARPS * 32, O_WARPS * 32);
+        }
+        if (s >= 0) {
+            // P4 tasks are split so that all warps finish together: the O warps take the first
+            // part, the last V warp (no P1 row) the next, the other V warps the rest.
+            const int n4 = (i_hi - i_lo) * (C::OUT_COLS / 2);
+            const int cut_a = min(n4, ((n4 * PH_CUT_A) / 32 + 31) & ~31);
+            const int cut_b = min(n4, ((n4 * PH_CUT_B) / 32 + 31) & ~31);
+            int t0, t1, nt;
+            if (warp >= V_WARPS) {
+                asm volatile("bar.sync 1, %0;" ::"n"(PH_NT) : "memory");
+                t0 = threadIdx.x - V_WARPS * 32; t1 = cut_a; nt = O_WARPS * 32;
+            } else {
+                asm volatile("bar.sync 2, %0;" ::"n"(V_WARPS * 32) : "memory");   // P3 done in all V warps
+                if (warp == V_WARPS - 1) { t0 = cut_a + (threadIdx.x & 31); t1 = cut_b; nt = 32; }
+                else { t0 = cut_b + threadIdx.x; t1 = n4; nt = (V_WARPS - 1) * 32; }
+            }
+            phase_solve<R>(a, g, U, V, M, m0, i_lo, i_hi, s_prod, st, t0, t1, nt);
         }
         __syncthreads();
         cur = nxt;
