@@ -35,17 +35,31 @@
 
 namespace ofb {
 
+#ifdef PH_PROF
+// Development aid: per-warp cycle totals of the first CTA, by region of the step loop.
+__device__ unsigned long long g_phase_prof[32 * 8];
+#define PH_MARK(slot)                                                            \
+    do {                                                                         \
+        const long long t_now = clock64();                                       \
+        prof_acc[slot] += t_now - prof_t;                                        \
+        prof_t = t_now;                                                          \
+    } while (0)
+#else
+#define PH_MARK(slot) do { } while (0)
+#endif
+
 namespace {
 
 #ifndef PH_CUT_A
-#define PH_CUT_A 32              // share (in 1/32) of the P4 tasks taken by the O warps ...
-#define PH_CUT_B 32              // ... and up to which the last V warp takes them
+#define PH_CUT_A 20              // share (in 1/32) of the P4 tasks taken by the O warps ...
+#define PH_CUT_B 26              // ... and up to which the last V warp takes them
 #endif
 constexpr int PH_NT = 512;       // threads per CTA (16 warps; a warp = one row of 32 quads)
 constexpr int PH_NW = PH_NT / 32;
 constexpr int PH_PC = 128;       // product columns per strip = 32 lanes x 4 columns
 constexpr int AB_HALF = 72;      // warped-frame rows: lo pairs [0,64), hi pairs [72,136)
 constexpr int AB_PITCH = 136;
+constexpr int HR_RING = 16;     // coarse-flow rows kept in shared memory: row k lives in slot (k + 2) & 15
 
 template <int R>
 struct PhaseCfg {
@@ -61,7 +75,7 @@ struct PhaseCfg {
     static constexpr int PPITCH = PHALF + 2 * OUT_LANES;
     static constexpr int PROD_D = WIN * 5 * PPITCH;
     static constexpr int AB_D = AB_ROWS * 2 * AB_PITCH;
-    static constexpr int HR_D = HR_ROWS * 2 * PH_PC;
+    static constexpr int HR_D = HR_RING * 2 * PH_PC;
     static constexpr int VS_D = 2 * R * 5 * PPITCH;   // suffix sums of the previous vertical block
     static constexpr size_t SMEM_BYTES = (size_t)(PROD_D + AB_D + HR_D + VS_D) * 8;
     static constexpr int VPAIRS = 2 * OUT_LANES;      // column pairs per channel in P3
@@ -110,7 +124,7 @@ template <int HR_ROWS>
 __device__ __forceinline__ void up_rows_issue(const LevelArgs& a, const PGeo& g, const double* __restrict__ cu,
                                               const double* __restrict__ cv, int ka, int nk, UpPre& q)
 {
-    static_assert(UP_K * PH_NT >= HR_ROWS * PH_PC, "UP_K too small");
+    static_assert(UP_K * PH_NT >= HR_ROWS * PH_PC && HR_ROWS <= HR_RING, "UP_K too small");
     const int wc = a.wc, hc = a.hc;
     const int j = (g.c0 >> 1) + (threadIdx.x & 63);
     const int p = (threadIdx.x >> 6) & 1;
@@ -152,7 +166,7 @@ __device__ __forceinline__ void up_rows_finish(const LevelArgs& a, const PGeo& g
                 o = pyrup_row(row, 0, 2 * j + 1, wc);
             }
         }
-        sts2(s_hr + (r * 2 + p) * PH_PC + 2 * jl, e, o);
+        sts2(s_hr + ((((ka + r + 2) & (HR_RING - 1)) * 2 + p) * PH_PC) + 2 * jl, e, o);
     }
 }
 
@@ -166,7 +180,7 @@ template <int R>
 __device__ __forceinline__ void phase_remap(const LevelArgs& a, const PGeo& g, const double* __restrict__ A,
                                             const double* __restrict__ B, double* __restrict__ U,
                                             double* __restrict__ V, int vy0, int r_first, int r_step, int sb,
-                                            int ka, const double* s_hr, double* s_ab)
+                                            const double* s_hr, double* s_ab)
 {
     using C = PhaseCfg<R>;
     const int W = g.W, H = g.H;
@@ -188,21 +202,22 @@ __device__ __forceinline__ void phase_remap(const LevelArgs& a, const PGeo& g, c
         if (g.has_coarse) {
             // vertical pass of cv::pyrUp from the rows of P0
             const int k = yy >> 1;
-            const double* hu = s_hr + ((k - ka) * 2) * PH_PC + lane;      // row k, plane u
+            const double* hm = s_hr + (((k + 1) & (HR_RING - 1)) * 2) * PH_PC + lane;   // row k-1, plane u
+            const double* h0 = s_hr + (((k + 2) & (HR_RING - 1)) * 2) * PH_PC + lane;   // row k
+            const double* hp = s_hr + (((k + 3) & (HR_RING - 1)) * 2) * PH_PC + lane;   // row k+1
             double upu[4], upv[4];
             if (yy & 1) {
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
-                    const double* h = hu + 32 * i;
-                    upu[i] = dmul(dmul(dadd(h[0], h[2 * PH_PC]), 4.0), 1.0 / 64.0);
-                    upv[i] = dmul(dmul(dadd(h[PH_PC], h[3 * PH_PC]), 4.0), 1.0 / 64.0);
+                    upu[i] = dmul(dmul(dadd(h0[32 * i], hp[32 * i]), 4.0), 1.0 / 64.0);
+                    upv[i] = dmul(dmul(dadd(h0[PH_PC + 32 * i], hp[PH_PC + 32 * i]), 4.0), 1.0 / 64.0);
                 }
             } else {
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
-                    const double* h = hu + 32 * i;
-                    upu[i] = dmul(dadd(dadd(h[-2 * PH_PC], dmul(h[0], 6.0)), h[2 * PH_PC]), 1.0 / 64.0);
-                    upv[i] = dmul(dadd(dadd(h[-PH_PC], dmul(h[PH_PC], 6.0)), h[3 * PH_PC]), 1.0 / 64.0);
+                    upu[i] = dmul(dadd(dadd(hm[32 * i], dmul(h0[32 * i], 6.0)), hp[32 * i]), 1.0 / 64.0);
+                    upv[i] = dmul(dadd(dadd(hm[PH_PC + 32 * i], dmul(h0[PH_PC + 32 * i], 6.0)), hp[PH_PC + 32 * i]),
+                                  1.0 / 64.0);
                 }
             }
             // park the upsampled flow of output pixels for the epilogue (tmpu += upu, :634-637)
@@ -577,26 +592,42 @@ __global__ void __launch_bounds__(PH_NT, 1) lk_level_phase_kernel(LevelArgs a, i
                                        : (1 + warp <= C::WIN - O_WARPS ? 1 + warp : (warp == V_WARPS - 1 ? 0 : -1));
     Step cur = step_geo(0);
     cur.any = false;
+    int k_have = -1000;                                // highest coarse row in the ring
+#ifdef PH_PROF
+    long long prof_acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    long long prof_t = clock64();
+#endif
     for (int s = -1; s < n_steps; ++s) {
         const Step nxt = step_geo(s + 1);
+        PH_MARK(7);
         {
+            // coarse rows of the next step that are not in the ring yet (consecutive steps overlap)
             UpPre q;
             const bool up = nxt.any && g.has_coarse;
-            if (up) up_rows_issue<C::HR_ROWS>(a, g, cu, cv, nxt.ka, nxt.nk, q);
+            const int k_from = max(nxt.ka, k_have + 1), n_new = nxt.ka + nxt.nk - k_from;
+            if (up) up_rows_issue<C::HR_ROWS>(a, g, cu, cv, k_from, n_new, q);
             if (s >= 0) phase_products<R>(g, cur.vy0, cur.sb, s_ab, s_prod);
-            if (up) up_rows_finish(a, g, cu, cv, nxt.ka, nxt.nk, q, s_hr);
+            if (up) {
+                up_rows_finish(a, g, cu, cv, k_from, n_new, q, s_hr);
+                k_have = nxt.ka + nxt.nk - 1;
+            }
         }
+        PH_MARK(0);
         __syncthreads();
+        PH_MARK(1);
         const int m0 = C::WIN * (s - 1) + 1;           // output row (relative to y0) of block row 0
         const int i_lo = max(0, -m0), i_hi = s >= 0 ? min(C::WIN, rows - m0) : 0;
         if (warp < V_WARPS && s >= 0) {
             if (v_task) phase_vertical<R>(s_prod + voff, s_vs + voff);
             asm volatile("bar.arrive 1, %0;" ::"n"(PH_NT) : "memory");
+            asm volatile("bar.sync 2, %0;" ::"n"(V_WARPS * 32) : "memory");   // P3 done in all V warps
         }
+        PH_MARK(2);
         {
             const int r_mine = nxt.any && my_row >= nxt.r_lo ? my_row : C::WIN + 1;
-            phase_remap<R>(a, g, A, B, U, V, nxt.vy0, r_mine, C::WIN + 1, nxt.sb, nxt.ka, s_hr, s_ab);
+            phase_remap<R>(a, g, A, B, U, V, nxt.vy0, r_mine, C::WIN + 1, nxt.sb, s_hr, s_ab);
         }
+        PH_MARK(3);
         if (s >= 0) {
             // P4 tasks are split so that all warps finish together: the O warps take the first
             // part, the last V warp (no P1 row) the next, the other V warps the rest.
@@ -608,15 +639,21 @@ __global__ void __launch_bounds__(PH_NT, 1) lk_level_phase_kernel(LevelArgs a, i
                 asm volatile("bar.sync 1, %0;" ::"n"(PH_NT) : "memory");
                 t0 = threadIdx.x - V_WARPS * 32; t1 = cut_a; nt = O_WARPS * 32;
             } else {
-                asm volatile("bar.sync 2, %0;" ::"n"(V_WARPS * 32) : "memory");   // P3 done in all V warps
                 if (warp == V_WARPS - 1) { t0 = cut_a + (threadIdx.x & 31); t1 = cut_b; nt = 32; }
                 else { t0 = cut_b + threadIdx.x; t1 = n4; nt = (V_WARPS - 1) * 32; }
             }
+            PH_MARK(4);
             phase_solve<R>(a, g, U, V, M, m0, i_lo, i_hi, s_prod, st, t0, t1, nt);
         }
+        PH_MARK(5);
         __syncthreads();
+        PH_MARK(6);
         cur = nxt;
     }
+#ifdef PH_PROF
+    if (blockIdx.x == 1 && blockIdx.y == 0 && blockIdx.z == 0 && (threadIdx.x & 31) == 0 && a.w >= 1920)
+        for (int i = 0; i < 8; ++i) atomicAdd(&g_phase_prof[warp * 8 + i], (unsigned long long)prof_acc[i]);
+#endif
 
     if (a.stats) {
 #pragma unroll
@@ -695,3 +732,15 @@ cudaError_t launch_lk_level_phase(const LevelArgs& a, int n_pairs, cudaStream_t 
 }
 
 }  // namespace ofb
+
+#ifdef PH_PROF
+extern "C" __attribute__((visibility("default"))) int of_b200_debug_phase_prof(unsigned long long* out, int reset)
+{
+    cudaError_t e = cudaMemcpyFromSymbol(out, ofb::g_phase_prof, sizeof(unsigned long long) * 32 * 8);
+    if (e == cudaSuccess && reset) {
+        static unsigned long long z[32 * 8];
+        e = cudaMemcpyToSymbol(ofb::g_phase_prof, z, sizeof(z));
+    }
+    return (int)e;
+}
+#endif

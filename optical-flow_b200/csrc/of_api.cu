@@ -215,7 +215,7 @@ struct TimedLaunch {
 
 cudaError_t launch_lk_level(of_ctx* ctx, const ofb::LevelArgs& a, int n_pairs, cudaStream_t s)
 {
-    if (ctx->force_variant == 4) {
+    if (ctx->force_variant == 0 || ctx->force_variant == 4) {
         bool handled = false;
         cudaError_t e = ofb::launch_lk_level_phase(a, n_pairs, s, &ctx->launches, &handled);
         if (handled || e != cudaSuccess) return e;
