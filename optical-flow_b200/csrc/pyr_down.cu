@@ -8,10 +8,12 @@
 // R = BORDER_REFLECT_101.  All frames of a batch (both frames of every pair, or every
 // frame of a stream) go through one launch: grid.z = image index.
 //
-// Each CTA produces a TX x TY output tile.  The (2TX+3) x (2TY+3) source patch is read
-// once with coalesced loads into shared memory, the horizontal pass is evaluated once per
-// (source row, output column) into a second shared plane, and the vertical pass reads that
-// plane -- so every source value crosses HBM/L2 once per CTA and `hor` is never recomputed.
+// Streaming kernel: a CTA owns 128 output columns and marches down a chunk of output rows; a
+// thread owns one output column and keeps the five horizontally filtered source rows of the
+// current output row in registers (two new source rows per output row).  A source row is read
+// once, as one 16-byte load per thread (columns 2x, 2x+1); the three neighbours come from the
+// adjacent lanes by shuffle, warp-edge and image-border lanes fetch theirs with scalar loads.
+// HBM traffic = the source once + the destination once (+ 3 extra source rows per chunk).
 #include "of_device.cuh"
 #include "of_kernels.h"
 
@@ -19,11 +21,8 @@ namespace ofb {
 
 namespace {
 
-constexpr int PD_TX = 64;   // output tile width
-constexpr int PD_TY = 8;    // output tile height
-constexpr int PD_NT = 256;
-constexpr int PD_SW = 2 * PD_TX + 3;  // source patch width
-constexpr int PD_SH = 2 * PD_TY + 3;  // source patch height
+constexpr int PD_NT = 128;      // threads = output columns per CTA
+constexpr int PD_AHEAD = 3;     // output rows whose source loads are in flight
 
 __device__ __forceinline__ int r101_any(int i, int n)
 {
@@ -34,49 +33,104 @@ __device__ __forceinline__ int r101_any(int i, int n)
     return i >= n ? p - i : i;
 }
 
-__global__ void __launch_bounds__(PD_NT) pyr_down_kernel(PyrDownArgs a)
-{
-    __shared__ double s_src[PD_SH][PD_SW + 1];
-    __shared__ double s_hor[PD_SH][PD_TX];
+struct PdCol {
+    int x;            // output column
+    int c[5];         // reflected source columns 2x-2 .. 2x+2
+    bool valid;       // x < ow
+    bool pair;        // columns 2x, 2x+1 both exist and can be read as one 16-byte load
+    bool fix_l, fix_r;   // left / right neighbours are not available from the adjacent lanes
+};
 
+// The thread's source values of one row: columns 2x, 2x+1 for every thread (the only loads of
+// interior lanes) plus, for warp-edge and image-border lanes, the neighbours that no adjacent
+// lane can supply.  Issued several rows ahead of their use.
+struct PdRow { double2 v; double e0, e1, e4; };
+
+__device__ __forceinline__ PdRow pd_load(const double* __restrict__ row, const PdCol& t)
+{
+    PdRow r;
+    r.v = make_double2(0.0, 0.0);
+    r.e0 = r.e1 = r.e4 = 0.0;
+    if (t.pair) {
+        r.v = __ldg(reinterpret_cast<const double2*>(row + t.c[2]));
+    } else if (t.valid) {
+        r.v.x = __ldg(row + t.c[2]);
+        r.v.y = __ldg(row + t.c[3]);
+    }
+    if (t.fix_l) { r.e0 = __ldg(row + t.c[0]); r.e1 = __ldg(row + t.c[1]); }
+    if (t.fix_r) r.e4 = __ldg(row + t.c[4]);
+    return r;
+}
+
+// Horizontal pass of one source row for this thread's output column.  Warp-collective.
+__device__ __forceinline__ double pd_hrow(const PdCol& t, const PdRow& r)
+{
+    const double s2 = r.v.x, s3 = r.v.y;
+    double s0 = __shfl_up_sync(0xffffffffu, s2, 1);
+    double s1 = __shfl_up_sync(0xffffffffu, s3, 1);
+    double s4 = __shfl_down_sync(0xffffffffu, s2, 1);
+    if (t.fix_l) { s0 = r.e0; s1 = r.e1; }
+    if (t.fix_r) s4 = r.e4;
+    double hv = dmul(s2, 6.0);
+    hv = dadd(hv, dmul(dadd(s1, s3), 4.0));
+    hv = dadd(hv, s0);
+    return dadd(hv, s4);
+}
+
+__global__ void __launch_bounds__(PD_NT) pyr_down_kernel(PyrDownArgs a, int rows_per_cta)
+{
     const int img = blockIdx.z;
     const double* __restrict__ src = a.src + (size_t)img * a.src_img_stride;
     double* __restrict__ dst = a.dst + (size_t)img * a.dst_img_stride;
-    const int ow = (a.w + 1) >> 1, oh = (a.h + 1) >> 1;
-    const int ox0 = blockIdx.x * PD_TX, oy0 = blockIdx.y * PD_TY;
-    const int sx0 = 2 * ox0 - 2, sy0 = 2 * oy0 - 2;
+    const int w = a.w, h = a.h;
+    const int ow = (w + 1) >> 1, oh = (h + 1) >> 1;
+    const int lane = threadIdx.x & 31;
 
-    // Source patch, reflect-101 applied at load time.
-    for (int i = threadIdx.x; i < PD_SH * PD_SW; i += PD_NT) {
-        const int ry = i / PD_SW, rx = i - ry * PD_SW;
-        const int y = r101_any(sy0 + ry, a.h), x = r101_any(sx0 + rx, a.w);
-        s_src[ry][rx] = __ldg(src + (size_t)y * a.src_pitch + x);
+    PdCol t;
+    t.x = blockIdx.x * PD_NT + threadIdx.x;
+    t.valid = t.x < ow;
+#pragma unroll
+    for (int k = 0; k < 5; ++k) t.c[k] = t.valid ? r101_any(2 * t.x - 2 + k, w) : 0;
+    const bool vec = ((reinterpret_cast<uintptr_t>(src) | (a.src_pitch * 8)) & 15) == 0;
+    t.pair = t.valid && vec && 2 * t.x + 1 < w;
+    // neighbours by shuffle need an adjacent lane that holds the true (unreflected) columns
+    t.fix_l = t.valid && (lane == 0 || t.x == 0);
+    t.fix_r = t.valid && (lane == 31 || 2 * t.x + 2 >= w || t.x + 1 >= ow);
+
+    const int oy0 = blockIdx.y * rows_per_cta;
+    const int oy1 = min(oy0 + rows_per_cta, oh);
+    auto row_ptr = [&](int y) { return src + (size_t)r101_any(y, h) * a.src_pitch; };
+    double h0, h1, h2, h3, h4;
+    {
+        const PdRow r2 = pd_load(row_ptr(2 * oy0 - 2), t), r3 = pd_load(row_ptr(2 * oy0 - 1), t);
+        const PdRow r4 = pd_load(row_ptr(2 * oy0), t);
+        h2 = pd_hrow(t, r2);
+        h3 = pd_hrow(t, r3);
+        h4 = pd_hrow(t, r4);
     }
-    __syncthreads();
-
-    // Horizontal pass: one value per (patch row, output column).
-    for (int i = threadIdx.x; i < PD_SH * PD_TX; i += PD_NT) {
-        const int ry = i / PD_TX, tx = i - ry * PD_TX;
-        const double* r = &s_src[ry][2 * tx];   // r[2] is source column 2*(ox0+tx)
-        double hv = dmul(r[2], 6.0);
-        hv = dadd(hv, dmul(dadd(r[1], r[3]), 4.0));
-        hv = dadd(hv, r[0]);
-        hv = dadd(hv, r[4]);
-        s_hor[ry][tx] = hv;
+    // software pipeline: the loads of PD_AHEAD output rows (2 source rows each) stay in flight
+    PdRow q[PD_AHEAD][2];
+#pragma unroll
+    for (int k = 0; k < PD_AHEAD; ++k) {
+        q[k][0] = pd_load(row_ptr(2 * (oy0 + k) + 1), t);
+        q[k][1] = pd_load(row_ptr(2 * (oy0 + k) + 2), t);
     }
-    __syncthreads();
-
-    // Vertical pass.
-    for (int i = threadIdx.x; i < PD_TY * PD_TX; i += PD_NT) {
-        const int ty = i / PD_TX, tx = i - ty * PD_TX;
-        const int oy = oy0 + ty, oxx = ox0 + tx;
-        if (oy >= oh || oxx >= ow) continue;
-        const int c = 2 * ty + 2;               // patch row of source row 2*oy
-        double o = dmul(s_hor[c][tx], 6.0);
-        o = dadd(o, dmul(dadd(s_hor[c - 1][tx], s_hor[c + 1][tx]), 4.0));
-        o = dadd(o, s_hor[c - 2][tx]);
-        o = dadd(o, s_hor[c + 2][tx]);
-        dst[(size_t)oy * a.dst_pitch + oxx] = dmul(o, 1.0 / 256.0);
+    for (int oyb = oy0; oyb < oy1; oyb += PD_AHEAD) {
+#pragma unroll
+        for (int k = 0; k < PD_AHEAD; ++k) {
+            const int oy = oyb + k;
+            const PdRow v1 = q[k][0], v2 = q[k][1];
+            q[k][0] = pd_load(row_ptr(2 * (oy + PD_AHEAD) + 1), t);      // reflected rows stay in range
+            q[k][1] = pd_load(row_ptr(2 * (oy + PD_AHEAD) + 2), t);
+            h0 = h2; h1 = h3; h2 = h4;
+            h3 = pd_hrow(t, v1);
+            h4 = pd_hrow(t, v2);
+            double o = dmul(h2, 6.0);
+            o = dadd(o, dmul(dadd(h1, h3), 4.0));
+            o = dadd(o, h0);
+            o = dadd(o, h4);
+            if (t.valid && oy < oy1) dst[(size_t)oy * a.dst_pitch + t.x] = dmul(o, 1.0 / 256.0);
+        }
     }
 }
 
@@ -85,8 +139,12 @@ __global__ void __launch_bounds__(PD_NT) pyr_down_kernel(PyrDownArgs a)
 cudaError_t launch_pyr_down(const PyrDownArgs& a, cudaStream_t s, unsigned long long* launches)
 {
     const int ow = (a.w + 1) / 2, oh = (a.h + 1) / 2;
-    dim3 grid((ow + PD_TX - 1) / PD_TX, (oh + PD_TY - 1) / PD_TY, a.n_images);
-    pyr_down_kernel<<<grid, PD_NT, 0, s>>>(a);
+    const int strips = (ow + PD_NT - 1) / PD_NT;
+    // rows per CTA: long enough to amortise the 3 warm-up rows, short enough to fill the GPU
+    int rows = 64;
+    while (rows > 16 && (long)strips * ((oh + rows - 1) / rows) * a.n_images < 148L * 12) rows /= 2;
+    dim3 grid(strips, (oh + rows - 1) / rows, a.n_images);
+    pyr_down_kernel<<<grid, PD_NT, 0, s>>>(a, rows);
     if (launches) *launches += 1;
     return cudaGetLastError();
 }

@@ -81,6 +81,22 @@ def test_random_inputs_vs_oracle(ofb, c_oracle, shape, r):
     check(got, c_oracle.coarse_to_fine(a, b, L, r, want_mask=True), r, "rand %s r=%d" % (shape, r))
 
 
+@pytest.mark.parametrize("variant", ["tile", "strip", "phase"])
+@pytest.mark.parametrize("r", [2, 5, 7])
+def test_every_level_kernel_vs_oracle(ofb, c_oracle, monkeypatch, variant, r):
+    """The library picks the level kernel itself (phase, else strip, else tile); OF_B200_VARIANT,
+    read when a context is created, pins one so that the fallbacks stay covered."""
+    monkeypatch.setenv("OF_B200_VARIANT", variant)
+    for h, w, L in [(120, 200, 4), (300, 34, 2), (96, 260, 3)]:
+        rng = np.random.default_rng(h * 7 + w + r)
+        base = rng.random((h + 8, w + 8))
+        a = base[4:4 + h, 4:4 + w].copy()
+        b = (0.6 * base[4:4 + h, 5:5 + w] + 0.4 * base[5:5 + h, 4:4 + w]) + rng.normal(0, 0.01, (h, w))
+        with ofb.Context(0, win_radius=r) as ctx:
+            got = ctx.coarseToFineEstimation(a, b, L, want_mask=True)
+        check(got, c_oracle.coarse_to_fine(a, b, L, r, want_mask=True), r, "%s %s r=%d" % (variant, (h, w, L), r))
+
+
 @pytest.mark.parametrize("r", [1, 7])
 @pytest.mark.parametrize("L", [1, 2, 4, 5])
 def test_table_pair_levels(ofb, c_oracle, table_pair, L, r):

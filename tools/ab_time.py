@@ -22,6 +22,10 @@ with ofb.Context(0, win_radius=r) as ctx:
     t = ctx.get_timing()
     l0 = [ms for k, l, ms in t if k == 1 and l == 0]; l1 = [ms for k, l, ms in t if k == 1 and l == 1]; l2 = [ms for k, l, ms in t if k == 1 and l == 2]
     ms = e0.elapsed_time(e1) / 10
+    other = {}
+    for k, l, m_ in t:
+        if k != 1: other[(k, l)] = other.get((k, l), 0.0) + m_ / 10
+    print("   other kernels (kind, level): ms/batch", {k: round(v, 4) for k, v in sorted(other.items())})
     print("%%-28s %%.3f ms/batch  %%8.1f pairs/s   L0 %%.3f  L1 %%.3f  L2 %%.3f  sum(u) %%.6f" %% (os.path.basename(os.environ.get("OF_B200_LIB", "default")), ms, n / ms * 1e3,
           sum(l0) / len(l0), sum(l1) / len(l1), sum(l2) / len(l2), float(U.sum())))
 ''' % ROOT
