@@ -273,6 +273,20 @@ def run_ours(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_val = world * pairs * e2e_steps / float(t.item())
     frame_bytes = H * W * 8
+    # the same call when only the per-pair gesture statistics come back (what the reference's
+    # live loop consumes, ParallelVideoPyr.cpp:845-905): the read-back shrinks to bytes per pair
+    ctx.flow_stream(fin, LEVELS, want_flow=False)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        _, _, stats_h = ctx.flow_stream(fin, LEVELS, want_flow=False)
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    t = torch.tensor([dt], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_stats_val = world * pairs * e2e_steps / float(t.item())
+    stats_bytes = int(stats_h.nbytes)
 
     if rank == 0:
         peak, peak_src = measured_peaks()
@@ -312,6 +326,9 @@ def run_ours(args):
             "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": (pairs + 1) * frame_bytes,
                     "d2h_bytes_per_step": 2 * pairs * frame_bytes, "steps": e2e_steps,
                     "api": "of_ctf_f64_stream (pinned host frames in, full u/v flow fields out)"},
+            "e2e_stats_only": {"value": e2e_stats_val, "unit": UNIT, "h2d_bytes_per_step": (pairs + 1) * frame_bytes,
+                               "d2h_bytes_per_step": stats_bytes,
+                               "api": "of_ctf_f64_stream, u = v = NULL: gesture statistics per pair only"},
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": roof,
