@@ -11,14 +11,18 @@
 // light per-element job, so latency is hidden by thread count instead of by deep per-warp
 // pipelines:
 //
-//   P0  horizontal pass of cv::pyrUp for the coarse-flow rows this step touches  -> HR
-//   P1  per pixel: vertical pass of pyrUp, float32 maps, 8 gathers, two blends   -> AB
+//   P0  horizontal pass of cv::pyrUp for the coarse-flow rows the next step needs     -> HR ring
+//   P1  one warp per fine row, a lane takes columns lane + 32 i: vertical pass of pyrUp,
+//       float32 maps, 8 coalesced gathers per pixel, two blends                       -> AB
 //       (the upsampled flow of output pixels is parked in u, v for the epilogue)
-//   P2  per pixel: 2x2 gradient stencils of both frames, five products           -> PROD
-//   P3  per (column, channel): vertical window sums, van Herk / Gil-Werman with the
-//       suffix sums of the previous block held in registers                      -> PROD
-//   P4a per (row, channel) warp line: horizontal window sums, registers+shuffles -> PROD
-//   P4b per output pixel: guarded solve, += parked up-flow, stores, mask, statistics
+//   P2  one warp per product row, a lane takes 4 columns: 2x2 gradient stencils of both
+//       frames, five products, horizontal window sums in registers + shuffles        -> PROD
+//   P3  per (channel, column pair): vertical window sums, van Herk / Gil-Werman; suffix
+//       sums of the previous block in shared memory, this block's rows in registers  -> PROD, VS
+//   P4  per (row, column pair): guarded solve, += parked up-flow, stores, mask, statistics
+//
+// The step loop at the bottom of the file overlaps the latency-bound P1 of the next step with
+// P3 and P4 of the current one (see the schedule comment there).
 //
 // Window sums never subtract: an all-zero window sums to exactly 0, so det == 0 pixels keep
 // the reference's "zero divisor -> 0" behaviour (cv::divide, :514,518) bit for bit.  The

@@ -1,4 +1,4 @@
-// Strip-marching fused pyramid-level kernel, V3 (throughput path), window radius R = 2..7.
+// Strip-marching fused pyramid-level kernel (warp-specialised; fallback of lk_level_phase.cu for calls without a flow output), window radius R = 2..7.
 //
 // One launch = one pyramid level of every pair of the batch, everything the reference does
 // between two levels (ParallelVideoPyr.cpp:610-703) plus the single-level LK (:327-542):

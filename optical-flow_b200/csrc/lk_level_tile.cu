@@ -18,7 +18,7 @@
 // SURVEY.md H7) sums rows first, then columns.
 //
 // This variant favours generality (runtime radius, levels smaller than a tile, 1-pixel
-// wide images); the strip-marching variant in lk_level_march.cu is the throughput path
+// wide images); the phase-synchronous kernel in lk_level_phase.cu is the throughput path
 // for the radii it is instantiated for.
 #include "of_device.cuh"
 #include "of_kernels.h"

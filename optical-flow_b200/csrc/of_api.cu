@@ -19,8 +19,6 @@
 namespace ofb {
 cudaError_t launch_lk_level_tile(const LevelArgs& a, int n_pairs, cudaStream_t s,
                                  unsigned long long* launches);
-cudaError_t launch_lk_level_march(const LevelArgs& a, int n_pairs, cudaStream_t s,
-                                  unsigned long long* launches, bool* handled);
 cudaError_t launch_lk_level_phase(const LevelArgs& a, int n_pairs, cudaStream_t s,
                                   unsigned long long* launches, bool* handled);
 cudaError_t launch_lk_level_strip(const LevelArgs& a, int n_pairs, cudaStream_t s,
@@ -53,7 +51,7 @@ struct of_ctx {
     Arena staging;                     // device copies of host-pointer inputs/outputs
     std::string err;
     unsigned long long launches = 0;
-    int force_variant = 0;             // 0 auto, 1 tile, 2 march, 3 strip, 4 phase (test hook via OF_B200_VARIANT)
+    int force_variant = 0;             // 0 auto, 1 tile, 3 strip, 4 phase (test hook via OF_B200_VARIANT)
     // optional per-launch device timing of the most recent batch call (bench roofline evidence)
     bool timing = false;
     std::vector<cudaEvent_t> tev;      // 2 events per timed launch
@@ -223,11 +221,6 @@ cudaError_t launch_lk_level(of_ctx* ctx, const ofb::LevelArgs& a, int n_pairs, c
     if (ctx->force_variant == 0 || ctx->force_variant == 3 || ctx->force_variant == 4) {
         bool handled = false;
         cudaError_t e = ofb::launch_lk_level_strip(a, n_pairs, s, &ctx->launches, &handled);
-        if (handled || e != cudaSuccess) return e;
-    }
-    if (ctx->force_variant == 2) {
-        bool handled = false;
-        cudaError_t e = ofb::launch_lk_level_march(a, n_pairs, s, &ctx->launches, &handled);
         if (handled || e != cudaSuccess) return e;
     }
     return ofb::launch_lk_level_tile(a, n_pairs, s, &ctx->launches);
@@ -410,7 +403,6 @@ of_status of_ctx_create(int device, const of_params* params, of_ctx** out)
     if (params) ctx->params = *params;
     if (const char* fv = getenv("OF_B200_VARIANT")) {
         if (!strcmp(fv, "tile")) ctx->force_variant = 1;
-        else if (!strcmp(fv, "march")) ctx->force_variant = 2;
         else if (!strcmp(fv, "strip")) ctx->force_variant = 3;
         else if (!strcmp(fv, "phase")) ctx->force_variant = 4;
     }
