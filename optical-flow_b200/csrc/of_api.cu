@@ -9,6 +9,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <string>
@@ -49,6 +50,8 @@ struct of_ctx {
     cudaEvent_t ev_down[2] = {nullptr, nullptr};
     Arena scratch;                     // pyramids + per-level flows
     Arena staging;                     // device copies of host-pointer inputs/outputs
+    of_gesture_stats* h_stats = nullptr;  // pinned host staging of the stream call's statistics
+    size_t h_stats_cap = 0;               // (a copy into pageable memory would block the host thread)
     std::string err;
     unsigned long long launches = 0;
     int force_variant = 0;             // 0 auto, 1 tile, 3 strip, 4 phase (test hook via OF_B200_VARIANT)
@@ -431,6 +434,7 @@ void of_ctx_destroy(of_ctx* ctx)
     cudaDeviceSynchronize();
     if (ctx->scratch.base) cudaFree(ctx->scratch.base);
     if (ctx->staging.base) cudaFree(ctx->staging.base);
+    if (ctx->h_stats) cudaFreeHost(ctx->h_stats);
     for (cudaEvent_t e : ctx->tev) cudaEventDestroy(e);
     for (int i = 0; i < 2; ++i) {
         if (ctx->ev_up[i]) cudaEventDestroy(ctx->ev_up[i]);
@@ -658,9 +662,18 @@ of_status of_ctf_f64_stream(of_ctx* ctx, const double* frames, int n_frames, siz
     const int n_pairs = n_frames - 1;
     const size_t pitch = align_up((size_t)width, 16);
     const size_t plane = align_up(pitch * height * sizeof(double), 256);
-    // chunk: about 256 MB of frames in flight per buffer, at most 16 pairs
+    // chunk: about 256 MB of frames in flight per buffer, at most 16 pairs -- and small enough
+    // that a call is cut into >= 8 chunks when it has the pairs for it: the upload of chunk
+    // i+1, the kernels of chunk i and the download of chunk i-1 run concurrently (three
+    // streams, two buffers), so only the first upload and the last download are exposed
     int C = (int)(((size_t)256 << 20) / plane);
     if (C > 16) C = 16;
+    if (C > (n_pairs + 7) / 8) C = (n_pairs + 7) / 8;
+    if (C < 2 && plane <= ((size_t)64 << 20)) C = 2;
+    if (const char* e = getenv("OF_B200_STREAM_CHUNK")) {      // development aid (tools/e2e_probe.py)
+        const int c = atoi(e);
+        if (c >= 1) C = c;
+    }
     if (C < 1) C = 1;
     if (C > n_pairs) C = n_pairs;
     const size_t in_bytes = plane * (C + 1);
@@ -669,6 +682,13 @@ of_status of_ctf_f64_stream(of_ctx* ctx, const double* frames, int n_frames, siz
     const size_t buf = in_bytes + out_bytes + st_bytes;
     st = arena_reserve(ctx, ctx->staging, 2 * buf);
     if (st) return st;
+    if (stats && ctx->h_stats_cap < (size_t)n_pairs) {
+        if (ctx->h_stats) cudaFreeHost(ctx->h_stats);
+        ctx->h_stats = nullptr;
+        ctx->h_stats_cap = 0;
+        OF_CUDA(ctx, cudaHostAlloc((void**)&ctx->h_stats, sizeof(of_gesture_stats) * (size_t)n_pairs, cudaHostAllocDefault));
+        ctx->h_stats_cap = (size_t)n_pairs;
+    }
     const size_t rowb = (size_t)width * sizeof(double);
     const bool dense_in = step_bytes == rowb && pitch * 8 == rowb && frame_stride_bytes == plane;
     const bool dense_out = u && uv_step_bytes == rowb && pitch * 8 == rowb;
@@ -683,13 +703,20 @@ of_status of_ctf_f64_stream(of_ctx* ctx, const double* frames, int n_frames, siz
         of_gesture_stats* d_st = (of_gesture_stats*)(base + in_bytes + out_bytes);
         const int p0 = i * C;
         const int np = (p0 + C <= n_pairs) ? C : n_pairs - p0;
-        // upload frames p0 .. p0+np
+        // upload frames p0 .. p0+np; frame p0 of a later chunk is already on the device (the
+        // last frame of the previous chunk, in the other buffer): device-to-device copy
         if (i >= 2) OF_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_stream, ctx->ev_done[bsel], 0));
         const char* src = (const char*)frames + (size_t)p0 * frame_stride_bytes;
+        const int k0 = i > 0 ? 1 : 0;
+        if (i > 0) {
+            const char* prev_last = ctx->staging.base + (1 - bsel) * buf + plane * (size_t)C;
+            OF_CUDA(ctx, cudaMemcpyAsync(d_in, prev_last, plane, cudaMemcpyDeviceToDevice, ctx->copy_stream));
+        }
         if (dense_in) {
-            OF_CUDA(ctx, cudaMemcpyAsync(d_in, src, plane * (np + 1), cudaMemcpyHostToDevice, ctx->copy_stream));
+            OF_CUDA(ctx, cudaMemcpyAsync((char*)d_in + k0 * plane, src + (size_t)k0 * frame_stride_bytes,
+                                         plane * (np + 1 - k0), cudaMemcpyHostToDevice, ctx->copy_stream));
         } else {
-            for (int k = 0; k <= np; ++k)
+            for (int k = k0; k <= np; ++k)
                 OF_CUDA(ctx, cudaMemcpy2DAsync((char*)d_in + k * plane, pitch * 8, src + (size_t)k * frame_stride_bytes,
                                                step_bytes, rowb, height, cudaMemcpyHostToDevice, ctx->copy_stream));
         }
@@ -722,13 +749,14 @@ of_status of_ctf_f64_stream(of_ctx* ctx, const double* frames, int n_frames, siz
             }
         }
         if (stats)
-            OF_CUDA(ctx, cudaMemcpyAsync(stats + p0, d_st, sizeof(of_gesture_stats) * np, cudaMemcpyDeviceToHost,
+            OF_CUDA(ctx, cudaMemcpyAsync(ctx->h_stats + p0, d_st, sizeof(of_gesture_stats) * np, cudaMemcpyDeviceToHost,
                                          ctx->down_stream));
         OF_CUDA(ctx, cudaEventRecord(ctx->ev_down[bsel], ctx->down_stream));
     }
     OF_CUDA(ctx, cudaStreamSynchronize(ctx->copy_stream));
     OF_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     OF_CUDA(ctx, cudaStreamSynchronize(ctx->down_stream));
+    if (stats) memcpy(stats, ctx->h_stats, sizeof(of_gesture_stats) * (size_t)n_pairs);
     return OF_OK;
 }
 
