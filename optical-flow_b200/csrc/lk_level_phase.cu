@@ -54,9 +54,9 @@ __device__ unsigned long long g_phase_prof[32 * 8];
 
 namespace {
 
-#ifndef PH_CUT_A
-#define PH_CUT_A 20              // share (in 1/32) of the P4 tasks taken by the O warps ...
-#define PH_CUT_B 26              // ... and up to which the last V warp takes them
+#ifndef PH_IDLE16
+#define PH_IDLE16 80             // head start (in 1/16 chunks of 32 P4 tasks) of a V warp without a P1 row ...
+#define PH_O16 18                // ... and of an O warp, over a V warp with a P1 row
 #endif
 constexpr int PH_NT = 512;       // threads per CTA (16 warps; a warp = one row of 32 quads)
 constexpr int PH_NW = PH_NT / 32;
@@ -213,8 +213,9 @@ __device__ __forceinline__ void phase_remap(const LevelArgs& a, const PGeo& g, c
             if (yy & 1) {
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
-                    upu[i] = dmul(dmul(dadd(h0[32 * i], hp[32 * i]), 4.0), 1.0 / 64.0);
-                    upv[i] = dmul(dmul(dadd(h0[PH_PC + 32 * i], hp[PH_PC + 32 * i]), 4.0), 1.0 / 64.0);
+                    // (a * 4) / 64 == a / 16: both scalings are exact
+                    upu[i] = dmul(dadd(h0[32 * i], hp[32 * i]), 1.0 / 16.0);
+                    upv[i] = dmul(dadd(h0[PH_PC + 32 * i], hp[PH_PC + 32 * i]), 1.0 / 16.0);
                 }
             } else {
 #pragma unroll
@@ -263,7 +264,7 @@ __device__ __forceinline__ void phase_remap(const LevelArgs& a, const PGeo& g, c
                 double sv[4][4];                             // 16 gathers, issued back to back
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
-                    const double* pa = F + tp[i].off;
+                    const double* pa = F + (unsigned)tp[i].off;     // off >= 0: one IMAD.WIDE.U32
                     sv[i][0] = __ldg(pa); sv[i][1] = __ldg(pa + 1);
                     sv[i][2] = __ldg(pa + pitch); sv[i][3] = __ldg(pa + pitch + 1);
                 }
@@ -633,21 +634,33 @@ __global__ void __launch_bounds__(PH_NT, 1) lk_level_phase_kernel(LevelArgs a, i
         }
         PH_MARK(3);
         if (s >= 0) {
-            // P4 tasks are split so that all warps finish together: the O warps take the first
-            // part, the last V warp (no P1 row) the next, the other V warps the rest.
+            // P4 tasks (row, column pair), in chunks of 32, are split so that all warps finish
+            // together: a V warp with a P1 row takes x chunks, an O warp (no P3) about one more,
+            // the V warps without a P1 row the rest (about five more each).
             const int n4 = (i_hi - i_lo) * (C::OUT_COLS / 2);
-            const int cut_a = min(n4, ((n4 * PH_CUT_A) / 32 + 31) & ~31);
-            const int cut_b = min(n4, ((n4 * PH_CUT_B) / 32 + 31) & ~31);
-            int t0, t1, nt;
+            const int nch = (n4 + 31) >> 5;
+            constexpr int N_VR = C::WIN - O_WARPS > 0 ? C::WIN - O_WARPS : 0;     // V warps with a P1 row
+            constexpr int N_VI = V_WARPS - N_VR;
+            const int x16 = max(0, 16 * nch - PH_IDLE16 * N_VI - PH_O16 * O_WARPS) / PH_NW;   // x in 1/16 chunks
+            const int q_vr = (x16 + 8) >> 4, q_o = (x16 + PH_O16 + 8) >> 4;
+            int c0, c1;
             if (warp >= V_WARPS) {
                 asm volatile("bar.sync 1, %0;" ::"n"(PH_NT) : "memory");
-                t0 = threadIdx.x - V_WARPS * 32; t1 = cut_a; nt = O_WARPS * 32;
+                c0 = (warp - V_WARPS) * q_o;
+                c1 = c0 + q_o;
+            } else if (warp < N_VR) {
+                c0 = O_WARPS * q_o + warp * q_vr;
+                c1 = c0 + q_vr;
             } else {
-                if (warp == V_WARPS - 1) { t0 = cut_a + (threadIdx.x & 31); t1 = cut_b; nt = 32; }
-                else { t0 = cut_b + threadIdx.x; t1 = n4; nt = (V_WARPS - 1) * 32; }
+                const int base = O_WARPS * q_o + N_VR * q_vr;
+                const int rest = max(0, nch - base), k = warp - N_VR;
+                c0 = base + (rest * k) / N_VI;
+                c1 = base + (rest * (k + 1)) / N_VI;
             }
+            c0 = min(c0, nch);
+            c1 = min(c1, nch);
             PH_MARK(4);
-            phase_solve<R>(a, g, U, V, M, m0, i_lo, i_hi, s_prod, st, t0, t1, nt);
+            phase_solve<R>(a, g, U, V, M, m0, i_lo, i_hi, s_prod, st, 32 * c0 + (threadIdx.x & 31), min(32 * c1, n4), 32);
         }
         PH_MARK(5);
         __syncthreads();
