@@ -156,6 +156,37 @@ OF_API of_status of_gesture_stats_dev(of_ctx *ctx, int n_pairs, const double *u,
 OF_API of_status of_pyr_down_f64_dev(of_ctx *ctx, const double *src, int width, int height,
                               size_t step_bytes, double *dst, size_t dst_step_bytes, void *stream);
 
+/* ---- live-loop pre-processing (the reference's main(), ParallelVideoPyr.cpp:791-813) ---- */
+
+/* Replaces: cvtColor(current_frame, current_frame, CV_BGR2GRAY)   ParallelVideoPyr.cpp:791.
+ * 8-bit interleaved BGR -> 8-bit gray, fixed point.  coeff_bits selects OpenCV's table:
+ * 14 = OpenCV 2.4 (the reference's library: 1868, 9617, 4899), 15 = OpenCV >= 3 (3735, 19235, 9798).
+ * Device pointers. */
+OF_API of_status of_bgr2gray_u8_dev(of_ctx *ctx, const unsigned char *bgr, int width, int height,
+                             size_t bgr_step_bytes, unsigned char *gray, size_t gray_step_bytes,
+                             int coeff_bits, void *stream);
+
+/* Replaces the block between the gray frame and the LK input of one live-loop iteration:
+ *   Mat diff = current_frame - LEARNING_RATE * prevFrame            :800  (8-bit, saturating)
+ *   threshold(diff, diff, DIFF_THRESH, 255, THRESH_TOZERO)           :803
+ *   Sobel(diff, .., CV_64FC1, 1, 0) + Sobel(diff, .., CV_64FC1, 0, 1) :808-811
+ *   dilate(diff, diff, Mat(), Point(-1,-1), 2); erode(.., 2)          :812-813
+ * cur_gray / prev_gray: 8-bit gray frames of the same size and step; out: double plane (the img2
+ * of this iteration's coarseToFineEstimation call, :832).  Reference constants: learning_rate 0.3,
+ * diff_thresh 10, morph_iterations 2 (1..4 supported).  Device pointers; one fused kernel. */
+OF_API of_status of_live_diff_f64_dev(of_ctx *ctx, const unsigned char *cur_gray,
+                               const unsigned char *prev_gray, int width, int height,
+                               size_t gray_step_bytes, double learning_rate, int diff_thresh,
+                               int morph_iterations, double *out, size_t out_step_bytes,
+                               void *stream);
+
+/* Host-pointer form of the two calls above (synchronous): cur / prev are 8-bit frames with
+ * `channels` = 1 (gray) or 3 (BGR, converted with coeff_bits first), out a host double plane. */
+OF_API of_status of_live_diff_f64(of_ctx *ctx, const unsigned char *cur, const unsigned char *prev,
+                           int channels, int width, int height, size_t frame_step_bytes,
+                           int coeff_bits, double learning_rate, int diff_thresh,
+                           int morph_iterations, double *out, size_t out_step_bytes);
+
 /* Blocks until everything queued on the context's own stream has finished. */
 OF_API of_status of_ctx_synchronize(of_ctx *ctx);
 

@@ -29,6 +29,7 @@ EXPORTS = (
     "of_ctf_f64", "of_ctf_f64_stream", "of_lk_single_f64_dev", "of_ctf_f64_dev",
     "of_ctf_f64_batch_dev", "of_gesture_stats_dev", "of_pyr_down_f64_dev",
     "of_ctx_synchronize", "of_ctx_launch_count", "of_ctx_set_timing", "of_ctx_get_timing",
+    "of_bgr2gray_u8_dev", "of_live_diff_f64_dev", "of_live_diff_f64",
 )
 
 
@@ -92,6 +93,9 @@ def lib():
                                        vp, sz, sz, vp, vp]
     L.of_gesture_stats_dev.argtypes = [vp, ci, vp, vp, sz, ci, ci, sz, vp, vp]
     L.of_pyr_down_f64_dev.argtypes = [vp, vp, ci, ci, sz, vp, sz, vp]
+    L.of_bgr2gray_u8_dev.argtypes = [vp, vp, ci, ci, sz, vp, sz, ci, vp]
+    L.of_live_diff_f64_dev.argtypes = [vp, vp, vp, ci, ci, sz, dbl, ci, ci, vp, sz, vp]
+    L.of_live_diff_f64.argtypes = [vp, vp, vp, ci, ci, ci, sz, ci, dbl, ci, ci, vp, sz]
     L.of_ctx_synchronize.argtypes = [vp]
     L.of_ctx_launch_count.argtypes = [vp]
     L.of_ctx_launch_count.restype = C.c_ulonglong
@@ -344,3 +348,39 @@ class Context:
         s = _stream_handle(stream, src.device)
         self._check(lib().of_pyr_down_f64_dev(self._h, src.data_ptr(), w, h, src.stride(0) * 8,
                                               dst.data_ptr(), dst.stride(0) * 8, s))
+
+    # ---- live-loop pre-processing (ParallelVideoPyr.cpp:791-813) ----
+    def live_diff(self, cur, prev, learning_rate: float = 0.3, diff_thresh: int = 10,
+                  morph_iterations: int = 2, coeff_bits: int = 14):
+        """The LK input of one live-loop iteration from two consecutive 8-bit frames (host arrays,
+        (H, W) gray or (H, W, 3) BGR): cvtColor :791, ``cur - 0.3 * prev`` :800, threshold :803,
+        Sobel x + Sobel y :808-811, dilate x2 / erode x2 :812-813.  Returns an (H, W) float64 array."""
+        cur = np.ascontiguousarray(cur)
+        prev = np.ascontiguousarray(prev)
+        if cur.dtype != np.uint8 or prev.dtype != np.uint8 or cur.shape != prev.shape or cur.ndim not in (2, 3):
+            raise BadArgError(OF_E_BADARG, "cur / prev must be uint8 arrays of the same (H, W) or (H, W, 3) shape")
+        ch = 1 if cur.ndim == 2 else cur.shape[2]
+        h, w = cur.shape[:2]
+        out = np.empty((h, w), np.float64)
+        self._check(lib().of_live_diff_f64(self._h, cur.ctypes.data, prev.ctypes.data, ch, w, h, w * ch,
+                                           coeff_bits, learning_rate, diff_thresh, morph_iterations,
+                                           out.ctypes.data, w * 8))
+        return out
+
+    def bgr2gray_dev(self, bgr, gray, coeff_bits: int = 14, stream=None):
+        """cvtColor(CV_BGR2GRAY) :791 on device tensors: bgr (H, W, 3) uint8 -> gray (H, W) uint8."""
+        h, w = gray.shape
+        s = _stream_handle(stream, bgr.device)
+        self._check(lib().of_bgr2gray_u8_dev(self._h, bgr.data_ptr(), w, h, bgr.stride(0), gray.data_ptr(),
+                                             gray.stride(0), coeff_bits, s))
+
+    def live_diff_dev(self, cur_gray, prev_gray, out, learning_rate: float = 0.3, diff_thresh: int = 10,
+                      morph_iterations: int = 2, stream=None):
+        """:800-813 on device tensors: two (H, W) uint8 gray frames -> out (H, W) float64."""
+        h, w = cur_gray.shape
+        if prev_gray.stride(0) != cur_gray.stride(0):
+            raise BadArgError(OF_E_BADARG, "cur_gray and prev_gray must share one row step")
+        s = _stream_handle(stream, cur_gray.device)
+        self._check(lib().of_live_diff_f64_dev(self._h, cur_gray.data_ptr(), prev_gray.data_ptr(), w, h,
+                                               cur_gray.stride(0), learning_rate, diff_thresh,
+                                               morph_iterations, out.data_ptr(), out.stride(0) * 8, s))

@@ -573,6 +573,95 @@ of_status of_pyr_down_f64_dev(of_ctx* ctx, const double* src, int width, int hei
     return OF_OK;
 }
 
+/* ---- live-loop pre-processing (ParallelVideoPyr.cpp:791-813) ------------------------------ */
+
+of_status of_bgr2gray_u8_dev(of_ctx* ctx, const unsigned char* bgr, int width, int height,
+                             size_t bgr_step_bytes, unsigned char* gray, size_t gray_step_bytes,
+                             int coeff_bits, void* stream)
+{
+    if (!ctx) return OF_E_BADARG;
+    if (!bgr || !gray || width < 1 || height < 1) return fail(ctx, OF_E_BADARG, "bad argument to of_bgr2gray_u8_dev");
+    if (bgr_step_bytes < (size_t)width * 3 || gray_step_bytes < (size_t)width) return fail(ctx, OF_E_BADARG, "bad step");
+    if (coeff_bits != 14 && coeff_bits != 15) return fail(ctx, OF_E_BADARG, "coeff_bits must be 14 (OpenCV 2.4) or 15 (OpenCV >= 3)");
+    OF_CUDA(ctx, cudaSetDevice(ctx->device));
+    OF_CUDA(ctx, ofb::launch_bgr2gray(bgr, bgr_step_bytes, gray, gray_step_bytes, width, height, coeff_bits,
+                                      pick(ctx, stream), &ctx->launches));
+    return OF_OK;
+}
+
+of_status of_live_diff_f64_dev(of_ctx* ctx, const unsigned char* cur_gray, const unsigned char* prev_gray,
+                               int width, int height, size_t gray_step_bytes, double learning_rate,
+                               int diff_thresh, int morph_iterations, double* out, size_t out_step_bytes,
+                               void* stream)
+{
+    if (!ctx) return OF_E_BADARG;
+    if (!cur_gray || !prev_gray || !out || width < 1 || height < 1)
+        return fail(ctx, OF_E_BADARG, "bad argument to of_live_diff_f64_dev");
+    if (gray_step_bytes < (size_t)width || out_step_bytes % 8 || out_step_bytes < (size_t)width * 8)
+        return fail(ctx, OF_E_BADARG, "bad step");
+    if (morph_iterations < 1 || morph_iterations > 4) return fail(ctx, OF_E_BADARG, "morph_iterations must be in 1..4");
+    if (!(learning_rate == learning_rate)) return fail(ctx, OF_E_BADARG, "learning_rate is NaN");
+    OF_CUDA(ctx, cudaSetDevice(ctx->device));
+    ofb::LiveDiffArgs a{};
+    a.cur = cur_gray;
+    a.prev = prev_gray;
+    a.gray_step = gray_step_bytes;
+    a.w = width;
+    a.h = height;
+    a.beta = (float)(-learning_rate);
+    a.thresh = diff_thresh;
+    a.iterations = morph_iterations;
+    a.out = out;
+    a.out_pitch = out_step_bytes / 8;
+    OF_CUDA(ctx, ofb::launch_live_diff(a, pick(ctx, stream), &ctx->launches));
+    return OF_OK;
+}
+
+of_status of_live_diff_f64(of_ctx* ctx, const unsigned char* cur, const unsigned char* prev, int channels,
+                           int width, int height, size_t frame_step_bytes, int coeff_bits,
+                           double learning_rate, int diff_thresh, int morph_iterations, double* out,
+                           size_t out_step_bytes)
+{
+    if (!ctx) return OF_E_BADARG;
+    if (!cur || !prev || !out || width < 1 || height < 1) return fail(ctx, OF_E_BADARG, "bad argument to of_live_diff_f64");
+    if (channels != 1 && channels != 3) return fail(ctx, OF_E_BADARG, "channels must be 1 (gray) or 3 (BGR)");
+    if (frame_step_bytes < (size_t)width * channels) return fail(ctx, OF_E_BADARG, "bad frame_step_bytes");
+    if (out_step_bytes % 8 || out_step_bytes < (size_t)width * 8) return fail(ctx, OF_E_BADARG, "bad out_step_bytes");
+    OF_CUDA(ctx, cudaSetDevice(ctx->device));
+    const size_t in_pitch = align_up((size_t)width * channels, 256);
+    const size_t g_pitch = align_up((size_t)width, 256);
+    const size_t o_pitch = align_up((size_t)width, 16);                  // doubles
+    const size_t in_plane = in_pitch * height, g_plane = g_pitch * height;
+    const size_t need = 2 * in_plane + 2 * g_plane + o_pitch * height * 8 + 1024;
+    of_status st = arena_reserve(ctx, ctx->staging, need);
+    if (st) return st;
+    unsigned char* d_in = (unsigned char*)ctx->staging.base;
+    unsigned char* d_g = d_in + 2 * in_plane;
+    double* d_out = (double*)(ctx->staging.base + align_up(2 * in_plane + 2 * g_plane, 256));
+    cudaStream_t s = ctx->stream;
+    const unsigned char* src[2] = {cur, prev};
+    const unsigned char* gray[2];
+    for (int k = 0; k < 2; ++k) {
+        OF_CUDA(ctx, cudaMemcpy2DAsync(d_in + k * in_plane, in_pitch, src[k], frame_step_bytes, (size_t)width * channels,
+                                       height, cudaMemcpyHostToDevice, s));
+        if (channels == 3) {
+            st = of_bgr2gray_u8_dev(ctx, d_in + k * in_plane, width, height, in_pitch, d_g + k * g_plane, g_pitch,
+                                    coeff_bits, s);
+            if (st) return st;
+            gray[k] = d_g + k * g_plane;
+        } else {
+            gray[k] = d_in + k * in_plane;
+        }
+    }
+    st = of_live_diff_f64_dev(ctx, gray[0], gray[1], width, height, channels == 3 ? g_pitch : in_pitch, learning_rate,
+                              diff_thresh, morph_iterations, d_out, o_pitch * 8, s);
+    if (st) return st;
+    OF_CUDA(ctx, cudaMemcpy2DAsync(out, out_step_bytes, d_out, o_pitch * 8, (size_t)width * 8, height,
+                                   cudaMemcpyDeviceToHost, s));
+    OF_CUDA(ctx, cudaStreamSynchronize(s));
+    return OF_OK;
+}
+
 /* ---- host-pointer entry points ------------------------------------------------------- */
 
 of_status of_ctf_f64(of_ctx* ctx, double* img1, double* img2, int width, int height,

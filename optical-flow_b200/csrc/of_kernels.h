@@ -70,6 +70,18 @@ struct StatsArgs {
     double mag_thresh;
 };
 
+struct LiveDiffArgs {         // live-loop pre-processing :800-813 (live_pre.cu)
+    const unsigned char* cur;
+    const unsigned char* prev;
+    size_t gray_step;         // bytes
+    int w, h;
+    float beta;               // (float)(-learning_rate)
+    int thresh;               // THRESH_TOZERO threshold
+    int iterations;           // dilate / erode iterations (1..4)
+    double* out;
+    size_t out_pitch;         // doubles
+};
+
 // Each returns the CUDA error of the launch and adds the number of kernels it launched
 // to *launches.
 cudaError_t launch_pyr_down(const PyrDownArgs& a, cudaStream_t s, unsigned long long* launches);
@@ -78,6 +90,9 @@ cudaError_t launch_lk_level(const LevelArgs& a, int n_pairs, cudaStream_t s,
 cudaError_t launch_warp_level(const WarpArgs& a, cudaStream_t s, unsigned long long* launches);
 cudaError_t launch_gesture_stats(const StatsArgs& a, int n_pairs, cudaStream_t s,
                                  unsigned long long* launches);
+cudaError_t launch_bgr2gray(const unsigned char* bgr, size_t bgr_step, unsigned char* gray, size_t gray_step, int w,
+                            int h, int bits, cudaStream_t s, unsigned long long* launches);
+cudaError_t launch_live_diff(const LiveDiffArgs& a, cudaStream_t s, unsigned long long* launches);
 cudaError_t launch_stats_finalize(of_gesture_stats* stats, int n_pairs, double count_thresh,
                                   cudaStream_t s, unsigned long long* launches);
 
