@@ -116,6 +116,18 @@ OF_API of_status of_ctf_f64_stream(of_ctx *ctx, const double *frames, int n_fram
                             double *u, double *v, size_t uv_pair_stride_bytes,
                             size_t uv_step_bytes, of_gesture_stats *stats);
 
+/* The same stream call for 8-bit frames (what imread(..., 0) / VideoCapture deliver): each frame is
+ * uploaded as bytes and converted on the device, pixel = rn(rn(v * alpha) + beta).
+ * Replaces: imread(...,0) frames + img.convertTo(img, CV_64FC1, 1.0/255)  ParallelBasicPyr.cpp:720-730
+ * (alpha = 1.0/255, beta = 0) followed by coarseToFineEstimation :753 per consecutive pair.
+ * step_bytes / frame_stride_bytes are in bytes of the 8-bit frames; 1/8 of the host-to-device
+ * traffic of of_ctf_f64_stream. */
+OF_API of_status of_ctf_u8_stream(of_ctx *ctx, const unsigned char *frames, int n_frames,
+                           size_t frame_stride_bytes, int width, int height,
+                           size_t step_bytes, double alpha, double beta, int n_levels,
+                           double *u, double *v, size_t uv_pair_stride_bytes,
+                           size_t uv_step_bytes, of_gesture_stats *stats);
+
 /* ---- device-pointer entry points (stream-ordered, asynchronous) -------------------------- */
 /* All pointers are device pointers on the context's device.  stream is a cudaStream_t passed
  * as void* (NULL = the context's own stream).  These are what the benchmark's device-resident

@@ -29,7 +29,7 @@ EXPORTS = (
     "of_ctf_f64", "of_ctf_f64_stream", "of_lk_single_f64_dev", "of_ctf_f64_dev",
     "of_ctf_f64_batch_dev", "of_gesture_stats_dev", "of_pyr_down_f64_dev",
     "of_ctx_synchronize", "of_ctx_launch_count", "of_ctx_set_timing", "of_ctx_get_timing",
-    "of_bgr2gray_u8_dev", "of_live_diff_f64_dev", "of_live_diff_f64",
+    "of_bgr2gray_u8_dev", "of_live_diff_f64_dev", "of_live_diff_f64", "of_ctf_u8_stream",
 )
 
 
@@ -87,6 +87,7 @@ def lib():
     L.of_lk_single_f64.argtypes = [vp, vp, vp, ci, ci, sz, vp, vp, sz, vp, sz]
     L.of_ctf_f64.argtypes = [vp, vp, vp, ci, ci, sz, ci, vp, vp, sz, vp, sz]
     L.of_ctf_f64_stream.argtypes = [vp, vp, ci, sz, ci, ci, sz, ci, vp, vp, sz, sz, vp]
+    L.of_ctf_u8_stream.argtypes = [vp, vp, ci, sz, ci, ci, sz, dbl, dbl, ci, vp, vp, sz, sz, vp]
     L.of_lk_single_f64_dev.argtypes = [vp, vp, vp, ci, ci, sz, vp, vp, sz, vp, sz, vp]
     L.of_ctf_f64_dev.argtypes = [vp, vp, vp, ci, ci, sz, ci, vp, vp, sz, vp, sz, vp]
     L.of_ctf_f64_batch_dev.argtypes = [vp, ci, vp, vp, sz, ci, ci, sz, ci, vp, vp, sz, sz,
@@ -250,19 +251,26 @@ class Context:
         return (u, v, m.astype(bool)) if want_mask else (u, v)
 
     def flow_stream(self, frames, nLevels: int, want_flow: bool = True, want_stats: bool = True,
-                    out_u=None, out_v=None):
+                    out_u=None, out_v=None, alpha: float = 1.0 / 255, beta: float = 0.0):
         """Host-pointer frame stream: ``frames`` (n, H, W) float64 (pinned memory makes the
         copies asynchronous) -> flows of the n-1 consecutive pairs and/or their gesture
         statistics (the live loop :769-905 without camera and window)."""
         f = np.asarray(frames)
-        if f.dtype != np.float64 or f.ndim != 3 or not f.flags.c_contiguous:
-            raise BadArgError(OF_E_BADARG, "frames must be a C-contiguous (n, H, W) float64 array")
+        if f.dtype not in (np.float64, np.uint8) or f.ndim != 3 or not f.flags.c_contiguous:
+            raise BadArgError(OF_E_BADARG, "frames must be a C-contiguous (n, H, W) float64 or uint8 array")
         n, h, w = f.shape
         u = v = None
         if want_flow:
             u = out_u if out_u is not None else np.empty((n - 1, h, w), np.float64)
             v = out_v if out_v is not None else np.empty((n - 1, h, w), np.float64)
         stats = np.zeros(n - 1, STATS_DTYPE) if want_stats else None
+        if f.dtype == np.uint8:      # 8-bit frames, converted on the device (convertTo(CV_64FC1, alpha, beta))
+            st = lib().of_ctf_u8_stream(self._h, f.ctypes.data, n, h * w, w, h, w, float(alpha), float(beta),
+                                        int(nLevels), u.ctypes.data if want_flow else None,
+                                        v.ctypes.data if want_flow else None, h * w * 8, w * 8,
+                                        stats.ctypes.data if want_stats else None)
+            self._check(st)
+            return u, v, stats
         st = lib().of_ctf_f64_stream(self._h, f.ctypes.data, n, h * w * 8, w, h, w * 8, int(nLevels),
                                      u.ctypes.data if want_flow else None,
                                      v.ctypes.data if want_flow else None, h * w * 8, w * 8,

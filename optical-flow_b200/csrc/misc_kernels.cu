@@ -97,4 +97,42 @@ cudaError_t launch_stats_finalize(of_gesture_stats* stats, int n_pairs, double c
     return cudaGetLastError();
 }
 
+// cv::Mat::convertTo(CV_64FC1, alpha, beta) of 8-bit frames (the harness mains' img.convertTo(img,
+// CV_64FC1, 1.0/255), ParallelBasicPyr.cpp:729-730): dst = rn(rn(v * alpha) + beta), v exact in double.
+// One thread = 4 consecutive pixels of one row.
+namespace {
+__global__ void __launch_bounds__(256) u8_to_f64_kernel(const unsigned char* __restrict__ src, size_t src_plane,
+                                                         size_t src_step, double* __restrict__ dst, size_t dst_plane,
+                                                         size_t dst_pitch, int w, int h, double alpha, double beta)
+{
+    const int x4 = (blockIdx.x * 64 + (threadIdx.x & 63)) * 4;
+    const int y = blockIdx.y * 4 + (threadIdx.x >> 6);
+    if (y >= h || x4 >= w) return;
+    const unsigned char* s = src + (size_t)blockIdx.z * src_plane + (size_t)y * src_step + x4;
+    double* d = dst + (size_t)blockIdx.z * dst_plane + (size_t)y * dst_pitch + x4;
+    if (x4 + 4 <= w && ((reinterpret_cast<uintptr_t>(s) & 3) | (reinterpret_cast<uintptr_t>(d) & 15)) == 0) {
+        const uint32_t p = __ldg(reinterpret_cast<const uint32_t*>(s));
+        double2 a, b;
+        a.x = dadd(dmul((double)(p & 255u), alpha), beta);
+        a.y = dadd(dmul((double)((p >> 8) & 255u), alpha), beta);
+        b.x = dadd(dmul((double)((p >> 16) & 255u), alpha), beta);
+        b.y = dadd(dmul((double)(p >> 24), alpha), beta);
+        reinterpret_cast<double2*>(d)[0] = a;
+        reinterpret_cast<double2*>(d)[1] = b;
+    } else {
+        for (int i = 0; i < 4 && x4 + i < w; ++i) d[i] = dadd(dmul((double)s[i], alpha), beta);
+    }
+}
+}  // namespace
+
+cudaError_t launch_u8_to_f64(const unsigned char* src, size_t src_plane, size_t src_step, double* dst, size_t dst_plane,
+                             size_t dst_pitch, int w, int h, int n_frames, double alpha, double beta, cudaStream_t s,
+                             unsigned long long* launches)
+{
+    dim3 grid((w + 255) / 256, (h + 3) / 4, n_frames);
+    u8_to_f64_kernel<<<grid, 256, 0, s>>>(src, src_plane, src_step, dst, dst_plane, dst_pitch, w, h, alpha, beta);
+    if (launches) *launches += 1;
+    return cudaGetLastError();
+}
+
 }  // namespace ofb

@@ -732,17 +732,22 @@ of_status of_lk_single_f64(of_ctx* ctx, const double* img1, const double* img2, 
                       step_bytes, 1, u, v, uv_step_bytes, mask, mask_step_bytes);
 }
 
-of_status of_ctf_f64_stream(of_ctx* ctx, const double* frames, int n_frames, size_t frame_stride_bytes,
-                            int width, int height, size_t step_bytes, int n_levels, double* u,
-                            double* v, size_t uv_pair_stride_bytes, size_t uv_step_bytes,
-                            of_gesture_stats* stats)
+}  // extern "C"
+
+// Frame stream, host pointers.  esz = 8: frames are doubles (of_ctf_f64_stream); esz = 1: frames
+// are 8-bit and become doubles on the device, v * alpha + beta (of_ctf_u8_stream).
+static of_status stream_impl(of_ctx* ctx, const void* frames, size_t esz, double alpha, double beta, int n_frames,
+                             size_t frame_stride_bytes, int width, int height, size_t step_bytes, int n_levels,
+                             double* u, double* v, size_t uv_pair_stride_bytes, size_t uv_step_bytes,
+                             of_gesture_stats* stats)
 {
-    of_status st = check_common(ctx, frames, frames, width, height, step_bytes, n_levels);
+    of_status st = esz == 8 ? check_common(ctx, (const double*)frames, (const double*)frames, width, height, step_bytes, n_levels)
+                            : check_common(ctx, (const double*)frames, (const double*)frames, width, height, 8 * step_bytes, n_levels);
     if (st) return st;
     if (n_frames < 2) return fail(ctx, OF_E_BADARG, "n_frames must be >= 2");
     if ((u == nullptr) != (v == nullptr)) return fail(ctx, OF_E_BADARG, "u and v must both be given or both be NULL");
     if (!u && !stats) return fail(ctx, OF_E_BADARG, "nothing to compute: u, v and stats are all NULL");
-    if (frame_stride_bytes % 8 || frame_stride_bytes < step_bytes * (size_t)(height - 1) + (size_t)width * 8)
+    if (frame_stride_bytes % esz || frame_stride_bytes < step_bytes * (size_t)(height - 1) + (size_t)width * esz)
         return fail(ctx, OF_E_BADARG, "bad frame_stride_bytes");
     if (u && (uv_step_bytes % 8 || uv_step_bytes < (size_t)width * 8 || uv_pair_stride_bytes % 8))
         return fail(ctx, OF_E_BADARG, "bad uv step/stride");
@@ -759,6 +764,9 @@ of_status of_ctf_f64_stream(of_ctx* ctx, const double* frames, int n_frames, siz
     if (C > 16) C = 16;
     if (C > (n_pairs + 7) / 8) C = (n_pairs + 7) / 8;
     if (C < 2 && plane <= ((size_t)64 << 20)) C = 2;
+    // 8-bit frames in, statistics out: the copies are small, so the chunk is sized for the kernels
+    // (full waves of the level kernel) instead of for copy/compute overlap
+    if (esz == 1 && !u) C = (int)(((size_t)256 << 20) / plane) < 16 ? (int)(((size_t)256 << 20) / plane) : 16;
     if (const char* e = getenv("OF_B200_STREAM_CHUNK")) {      // development aid (tools/e2e_probe.py)
         const int c = atoi(e);
         if (c >= 1) C = c;
@@ -768,7 +776,9 @@ of_status of_ctf_f64_stream(of_ctx* ctx, const double* frames, int n_frames, siz
     const size_t in_bytes = plane * (C + 1);
     const size_t out_bytes = u ? plane * C * 2 : 0;
     const size_t st_bytes = align_up(sizeof(of_gesture_stats) * C, 256);
-    const size_t buf = in_bytes + out_bytes + st_bytes;
+    const size_t plane8 = align_up((size_t)width * height, 256);       // 8-bit staging frames, dense rows
+    const size_t raw_bytes = esz == 1 ? plane8 * (C + 1) : 0;
+    const size_t buf = in_bytes + out_bytes + st_bytes + raw_bytes;
     st = arena_reserve(ctx, ctx->staging, 2 * buf);
     if (st) return st;
     if (stats && ctx->h_stats_cap < (size_t)n_pairs) {
@@ -779,7 +789,7 @@ of_status of_ctf_f64_stream(of_ctx* ctx, const double* frames, int n_frames, siz
         ctx->h_stats_cap = (size_t)n_pairs;
     }
     const size_t rowb = (size_t)width * sizeof(double);
-    const bool dense_in = step_bytes == rowb && pitch * 8 == rowb && frame_stride_bytes == plane;
+    const bool dense_in = esz == 8 && step_bytes == rowb && pitch * 8 == rowb && frame_stride_bytes == plane;
     const bool dense_out = u && uv_step_bytes == rowb && pitch * 8 == rowb;
 
     const int n_chunks = (n_pairs + C - 1) / C;
@@ -801,7 +811,21 @@ of_status of_ctf_f64_stream(of_ctx* ctx, const double* frames, int n_frames, siz
             const char* prev_last = ctx->staging.base + (1 - bsel) * buf + plane * (size_t)C;
             OF_CUDA(ctx, cudaMemcpyAsync(d_in, prev_last, plane, cudaMemcpyDeviceToDevice, ctx->copy_stream));
         }
-        if (dense_in) {
+        if (esz == 1) {
+            // 8-bit frames: upload (1/8 of the bytes), then convertTo(CV_64FC1, alpha, beta) on the device
+            unsigned char* d_raw = (unsigned char*)(base + in_bytes + out_bytes + st_bytes);
+            if (step_bytes == (size_t)width && frame_stride_bytes == plane8) {
+                OF_CUDA(ctx, cudaMemcpyAsync(d_raw + k0 * plane8, src + (size_t)k0 * frame_stride_bytes,
+                                             plane8 * (np + 1 - k0), cudaMemcpyHostToDevice, ctx->copy_stream));
+            } else {
+                for (int k = k0; k <= np; ++k)
+                    OF_CUDA(ctx, cudaMemcpy2DAsync(d_raw + k * plane8, width, src + (size_t)k * frame_stride_bytes,
+                                                   step_bytes, width, height, cudaMemcpyHostToDevice, ctx->copy_stream));
+            }
+            OF_CUDA(ctx, ofb::launch_u8_to_f64(d_raw + k0 * plane8, plane8, (size_t)width, (double*)((char*)d_in + k0 * plane),
+                                               plane / 8, pitch, width, height, np + 1 - k0, alpha, beta,
+                                               ctx->copy_stream, &ctx->launches));
+        } else if (dense_in) {
             OF_CUDA(ctx, cudaMemcpyAsync((char*)d_in + k0 * plane, src + (size_t)k0 * frame_stride_bytes,
                                          plane * (np + 1 - k0), cudaMemcpyHostToDevice, ctx->copy_stream));
         } else {
@@ -847,6 +871,27 @@ of_status of_ctf_f64_stream(of_ctx* ctx, const double* frames, int n_frames, siz
     OF_CUDA(ctx, cudaStreamSynchronize(ctx->down_stream));
     if (stats) memcpy(stats, ctx->h_stats, sizeof(of_gesture_stats) * (size_t)n_pairs);
     return OF_OK;
+}
+
+extern "C" {
+
+of_status of_ctf_f64_stream(of_ctx* ctx, const double* frames, int n_frames, size_t frame_stride_bytes,
+                            int width, int height, size_t step_bytes, int n_levels, double* u,
+                            double* v, size_t uv_pair_stride_bytes, size_t uv_step_bytes,
+                            of_gesture_stats* stats)
+{
+    return stream_impl(ctx, frames, 8, 1.0, 0.0, n_frames, frame_stride_bytes, width, height, step_bytes, n_levels, u, v,
+                       uv_pair_stride_bytes, uv_step_bytes, stats);
+}
+
+of_status of_ctf_u8_stream(of_ctx* ctx, const unsigned char* frames, int n_frames, size_t frame_stride_bytes,
+                           int width, int height, size_t step_bytes, double alpha, double beta, int n_levels,
+                           double* u, double* v, size_t uv_pair_stride_bytes, size_t uv_step_bytes,
+                           of_gesture_stats* stats)
+{
+    if (ctx && (!(alpha == alpha) || !(beta == beta))) return fail(ctx, OF_E_BADARG, "alpha / beta is NaN");
+    return stream_impl(ctx, frames, 1, alpha, beta, n_frames, frame_stride_bytes, width, height, step_bytes, n_levels, u, v,
+                       uv_pair_stride_bytes, uv_step_bytes, stats);
 }
 
 }  // extern "C"

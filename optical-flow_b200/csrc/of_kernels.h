@@ -93,6 +93,10 @@ cudaError_t launch_gesture_stats(const StatsArgs& a, int n_pairs, cudaStream_t s
 cudaError_t launch_bgr2gray(const unsigned char* bgr, size_t bgr_step, unsigned char* gray, size_t gray_step, int w,
                             int h, int bits, cudaStream_t s, unsigned long long* launches);
 cudaError_t launch_live_diff(const LiveDiffArgs& a, cudaStream_t s, unsigned long long* launches);
+// frames of 8-bit pixels (dense planes src_plane bytes apart) -> double planes (dst_plane doubles apart)
+cudaError_t launch_u8_to_f64(const unsigned char* src, size_t src_plane, size_t src_step, double* dst, size_t dst_plane,
+                             size_t dst_pitch, int w, int h, int n_frames, double alpha, double beta, cudaStream_t s,
+                             unsigned long long* launches);
 cudaError_t launch_stats_finalize(of_gesture_stats* stats, int n_pairs, double count_thresh,
                                   cudaStream_t s, unsigned long long* launches);
 

@@ -267,6 +267,41 @@ def test_host_stream_entry_point_pacman(ofb, c_oracle):
         assert bool(S["detected"][k]) == s["detected"]
 
 
+def test_u8_stream_entry_point(ofb, c_oracle, table_pair):
+    """8-bit frames in, converted on the device like the harness mains' convertTo(CV_64FC1, 1.0/255)
+    (ParallelBasicPyr.cpp:729-730: a multiplication by the double 1.0/255), then the stream call."""
+    raw = np.load(os.path.join(GOLDEN, "pacman_gray.npz"))["frames"][40:52]
+    assert raw.dtype == np.uint8
+    fr = raw.astype(np.float64) * (1.0 / 255)
+    L = ofb.getMaxLayer(240, 160)
+    with ofb.Context(0, mag_thresh=1.0, count_thresh=50) as ctx:
+        U, V, S = ctx.flow_stream(raw, L)
+        U2, V2, S2 = ctx.flow_stream(fr, L)
+        # ragged rows (a ROI of a wider 8-bit image) and a shift
+        wide = np.zeros((3, 160, 256), np.uint8)
+        wide[:, :, :240] = raw[:3]
+        st = np.zeros(2, ofb.STATS_DTYPE)
+        u = np.empty((2, 160, 240)); v = np.empty((2, 160, 240))
+        ctx._check(ofb.lib().of_ctf_u8_stream(ctx._h, wide.ctypes.data, 3, 160 * 256, 240, 160, 256, 0.5, -3.0, L,
+                                              u.ctypes.data, v.ctypes.data, 160 * 240 * 8, 240 * 8, st.ctypes.data))
+    assert np.array_equal(U, U2) and np.array_equal(V, V2) and np.array_equal(S, S2)
+    for k in range(len(raw) - 1):
+        uo, vo = c_oracle.coarse_to_fine(fr[k], fr[k + 1], L)
+        assert np.array_equal(U[k], uo) and np.array_equal(V[k], vo), "pair %d" % k
+    g = raw[:3].astype(np.float64) * 0.5 + (-3.0)
+    for k in range(2):
+        uo, vo = c_oracle.coarse_to_fine(g[k], g[k + 1], L)
+        assert np.array_equal(u[k], uo) and np.array_equal(v[k], vo), "shifted pair %d" % k
+    # KAT-7 from the 8-bit table crop: within the reference's own 1e-6 of its goldens
+    d = np.load(os.path.join(GOLDEN, "table_pair.npz"))
+    pair = np.stack([d["img1"], d["img2"]]).astype(np.uint8)
+    with ofb.Context(0) as ctx:
+        U, V, _ = ctx.flow_stream(pair, 7, want_stats=False)
+    gold = np.load(os.path.join(GOLDEN, "kat_golden.npz"))
+    assert np.abs(U[0] - gold["UPyrTest"] / 1e6).max() <= 1e-6     # ParallelBasicPyr.cpp:787
+    assert np.abs(V[0] - gold["VPyrTest"] / 1e6).max() <= 1e-6
+
+
 def test_hand_pair_config0(ofb, c_oracle):
     """BASELINE config 0: hand1 -> hand2 (3264x2448, EXIF ignored as OpenCV 2.4 did),
     L = getMaxLayer = 5, the reference's 3x3 window."""
