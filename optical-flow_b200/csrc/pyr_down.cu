@@ -134,11 +134,109 @@ __global__ void __launch_bounds__(PD_NT) pyr_down_kernel(PyrDownArgs a, int rows
     }
 }
 
+// ------------------------------------------------------------------------------ fast path
+// Even width, 16-byte aligned rows, at least 2 output columns.  Same arithmetic and operation
+// order as above, different thread mapping: a lane loads one 16-byte chunk (source columns 2k,
+// 2k+1) per source row and nothing else; lanes 1..30 of a warp own output columns, lanes 0 and 31
+// only supply their chunk to the neighbour (the chunk is loaded again by the adjacent warp, an L1 /
+// L2 hit), so a row costs one load instruction per warp, a thread keeps 4 registers per row in
+// flight, and 8 CTAs of 128 threads fit an SM with PDF_AHEAD x 2 rows x 16 B in flight per thread.
+constexpr int PDF_AHEAD = 4;
+constexpr int PDF_WCOLS = 30;                       // output columns per warp
+constexpr int PDF_COLS = PDF_WCOLS * (PD_NT / 32);  // per CTA
+
+__device__ __forceinline__ double2 pdf_load(const double* __restrict__ row, int k, bool have)
+{
+    return have ? __ldg(reinterpret_cast<const double2*>(row) + k) : make_double2(0.0, 0.0);
+}
+
+__device__ __forceinline__ double pdf_hrow(double2 v, bool first, bool last)
+{
+    const double s2 = v.x, s3 = v.y;
+    double s0 = __shfl_up_sync(0xffffffffu, s2, 1);
+    double s1 = __shfl_up_sync(0xffffffffu, s3, 1);
+    double s4 = __shfl_down_sync(0xffffffffu, s2, 1);
+    if (last) s4 = s2;                              // column w reflects to w-2 = 2x
+    if (first) { s0 = s4; s1 = s3; }                // columns -2, -1 reflect to 2, 1
+    double hv = dmul(s2, 6.0);
+    hv = dadd(hv, dmul(dadd(s1, s3), 4.0));
+    hv = dadd(hv, s0);
+    return dadd(hv, s4);
+}
+
+__global__ void __launch_bounds__(PD_NT, 8) pyr_down_fast_kernel(PyrDownArgs a, int rows_per_cta)
+{
+    const int img = blockIdx.z;
+    const double* __restrict__ src = a.src + (size_t)img * a.src_img_stride;
+    double* __restrict__ dst = a.dst + (size_t)img * a.dst_img_stride;
+    const int h = a.h;
+    const int ow = a.w >> 1, oh = (h + 1) >> 1;
+    const int lane = threadIdx.x & 31;
+    const int x = blockIdx.x * PDF_COLS + (threadIdx.x >> 5) * PDF_WCOLS + lane - 1;   // chunk = output column
+    const bool have = x >= 0 && x < ow;
+    const bool owner = have && lane >= 1 && lane <= PDF_WCOLS;
+    const bool first = x == 0, last = x == ow - 1;
+
+    const int oy0 = blockIdx.y * rows_per_cta;
+    const int oy1 = min(oy0 + rows_per_cta, oh);
+    const int per = h > 1 ? 2 * (h - 1) : 1;
+    auto row_ptr = [&](int y) {                     // BORDER_REFLECT_101, any y
+        int i = y % per;
+        if (i < 0) i += per;
+        if (i >= h) i = per - i;
+        return src + (size_t)i * a.src_pitch;
+    };
+    double h0, h1, h2, h3, h4;
+    {
+        const double2 r2 = pdf_load(row_ptr(2 * oy0 - 2), x, have), r3 = pdf_load(row_ptr(2 * oy0 - 1), x, have);
+        const double2 r4 = pdf_load(row_ptr(2 * oy0), x, have);
+        h2 = pdf_hrow(r2, first, last);
+        h3 = pdf_hrow(r3, first, last);
+        h4 = pdf_hrow(r4, first, last);
+    }
+    double2 q[PDF_AHEAD][2];
+#pragma unroll
+    for (int k = 0; k < PDF_AHEAD; ++k) {
+        q[k][0] = pdf_load(row_ptr(2 * (oy0 + k) + 1), x, have);
+        q[k][1] = pdf_load(row_ptr(2 * (oy0 + k) + 2), x, have);
+    }
+    double* out = dst + (size_t)oy0 * a.dst_pitch + x;
+    for (int oyb = oy0; oyb < oy1; oyb += PDF_AHEAD) {
+#pragma unroll
+        for (int k = 0; k < PDF_AHEAD; ++k) {
+            const int oy = oyb + k;
+            const double2 v1 = q[k][0], v2 = q[k][1];
+            q[k][0] = pdf_load(row_ptr(2 * (oy + PDF_AHEAD) + 1), x, have);
+            q[k][1] = pdf_load(row_ptr(2 * (oy + PDF_AHEAD) + 2), x, have);
+            h0 = h2; h1 = h3; h2 = h4;
+            h3 = pdf_hrow(v1, first, last);
+            h4 = pdf_hrow(v2, first, last);
+            double o = dmul(h2, 6.0);
+            o = dadd(o, dmul(dadd(h1, h3), 4.0));
+            o = dadd(o, h0);
+            o = dadd(o, h4);
+            if (owner && oy < oy1) *out = dmul(o, 1.0 / 256.0);
+            out += a.dst_pitch;
+        }
+    }
+}
+
 }  // namespace
 
 cudaError_t launch_pyr_down(const PyrDownArgs& a, cudaStream_t s, unsigned long long* launches)
 {
     const int ow = (a.w + 1) / 2, oh = (a.h + 1) / 2;
+#ifndef PD_NO_FAST
+    if ((a.w & 1) == 0 && a.w >= 4 && (((uintptr_t)a.src | (a.src_pitch * 8) | (a.src_img_stride * 8)) & 15) == 0) {
+        const int strips = (ow + PDF_COLS - 1) / PDF_COLS;
+        int rows = 64;
+        while (rows > 16 && (long)strips * ((oh + rows - 1) / rows) * a.n_images < 148L * 16) rows /= 2;
+        dim3 grid(strips, (oh + rows - 1) / rows, a.n_images);
+        pyr_down_fast_kernel<<<grid, PD_NT, 0, s>>>(a, rows);
+        if (launches) *launches += 1;
+        return cudaGetLastError();
+    }
+#endif
     const int strips = (ow + PD_NT - 1) / PD_NT;
     // rows per CTA: long enough to amortise the 3 warm-up rows, short enough to fill the GPU
     int rows = 64;
