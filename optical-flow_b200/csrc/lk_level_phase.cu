@@ -85,6 +85,25 @@ struct PhaseCfg {
     static constexpr int VPAIRS = 2 * OUT_LANES;      // column pairs per channel in P3
 };
 
+// R = 1 (the reference's own 3x3 window, get_Sum9 :114-160): the nine terms are summed in the
+// reference's row-major order, which is not separable, so there are no horizontal / vertical
+// passes.  A step is WIN = 15 rows (not the window length); raw products of all 128 strip
+// columns are kept in a ring of WIN + 2 rows laid out like the warped-frame rows.
+template <>
+struct PhaseCfg<1> {
+    static constexpr int HL = 1;
+    static constexpr int OUT_LANES = 30;
+    static constexpr int OUT_COLS = 4 * OUT_LANES;
+    static constexpr int WIN = 15;                    // rows per step
+    static constexpr int AB_ROWS = WIN + 1;
+    static constexpr int HR_ROWS = (WIN + 1) / 2 + 3;
+    static constexpr int PR_ROWS = WIN + 2;           // product-row ring
+    static constexpr int PROD_D = PR_ROWS * 5 * 136;
+    static constexpr int AB_D = AB_ROWS * 2 * 136;
+    static constexpr int HR_D = HR_RING * 2 * PH_PC;
+    static constexpr size_t SMEM_BYTES = (size_t)(PROD_D + AB_D + HR_D) * 8;
+};
+
 // Shared-memory rows that are read four columns per lane are "pair-split": columns 4j, 4j+1 of
 // lane j sit at lo[2j], columns 4j+2, 4j+3 at hi[2j] = row[half + 2j], so that every 128-bit
 // access of a warp is contiguous.  half = 8 (mod 16) doubles makes the column-per-lane and
@@ -270,7 +289,9 @@ __device__ __forceinline__ void phase_remap(const LevelArgs& a, const PGeo& g, c
                 }
                 double* v = f ? vb : va;
 #pragma unroll
-                for (int i = 0; i < 4; ++i) v[i] = blend4(sv[i][0], sv[i][1], sv[i][2], sv[i][3], tp[i].fr);
+                for (int i = 0; i < 4; ++i)
+                    v[i] = R == 1 ? blend4_exact(sv[i][0], sv[i][1], sv[i][2], sv[i][3], tp[i].fr)
+                                  : blend4(sv[i][0], sv[i][1], sv[i][2], sv[i][3], tp[i].fr);
                 if (!all_in) {                               // rare: a tap outside the image, non-finite map
 #pragma unroll
                     for (int i = 0; i < 4; ++i) {
@@ -422,6 +443,83 @@ __device__ __forceinline__ void phase_vertical(double* col, double* vs)
 // t_begin, t_begin + nthr, ... < t_end of the (i_hi - i_lo) * OUT_COLS / 2 tasks.
 struct StatAcc { unsigned long long x, y, c; };
 
+// Solve + epilogue of output pixels (y, xb), (y, xb + 1) from their five window sums.
+template <int R>
+__device__ __forceinline__ void solve_pair(const LevelArgs& a, const PGeo& g, double* __restrict__ U,
+                                           double* __restrict__ V, unsigned char* __restrict__ M, int y, int xb,
+                                           double2 sxx, double2 syy, double2 sxy, double2 sxt, double2 syt,
+                                           double det_eps, double mag2, StatAcc& st)
+{
+    const int W = g.W, H = g.H;
+    double* pu = U + (size_t)y * a.uv_pitch + xb;
+    double* pv = V + (size_t)y * a.uv_pitch + xb;
+    double upu[2] = {0.0, 0.0}, upv[2] = {0.0, 0.0};
+    if (g.has_coarse) {                                  // parked by P1 (same CTA, barriers between)
+        if (g.vec_uv) {
+            const double2 u0 = *reinterpret_cast<const double2*>(pu), v0 = *reinterpret_cast<const double2*>(pv);
+            upu[0] = u0.x; upu[1] = u0.y; upv[0] = v0.x; upv[1] = v0.y;
+        } else {
+            upu[0] = pu[0]; upu[1] = pu[1]; upv[0] = pv[0]; upv[1] = pv[1];
+        }
+    }
+    const bool yin = y >= R && y <= H - 1 - R;
+    double lu[2], lv[2], nus[2], nvs[2], dets[2];
+    unsigned okbits = 0;
+    bool fast = true;
+#pragma unroll
+    for (int q = 0; q < 2; ++q) {
+        const int x = xb + q;
+        const bool interior = yin && x >= R && x <= W - 1 - R;
+        const double xx = q ? sxx.y : sxx.x, yy = q ? syy.y : syy.x, xy = q ? sxy.y : sxy.x;
+        const double xt = q ? sxt.y : sxt.x, yt = q ? syt.y : syt.x;
+        dets[q] = dsub(dmul(xx, yy), dmul(xy, xy));
+        nus[q] = dsub(dmul(xy, yt), dmul(yy, xt));
+        nvs[q] = dsub(dmul(xt, xy), dmul(xx, yt));
+        const bool ok = interior && fabs(dets[q]) > det_eps;
+        okbits |= ok ? (1u << q) : 0u;
+        fast = (div2_fast(nus[q], nvs[q], dets[q], lu[q], lv[q]) || !ok) && fast;
+    }
+    if (!fast) {                                         // rare: exponent range outside the fast path
+#pragma unroll
+        for (int q = 0; q < 2; ++q) {
+            if ((okbits >> q) & 1u) {
+                lu[q] = ddiv_slow(nus[q], dets[q]);
+                lv[q] = ddiv_slow(nvs[q], dets[q]);
+            }
+        }
+    }
+    double fu[2], fv[2];
+#pragma unroll
+    for (int q = 0; q < 2; ++q) {
+        const bool ok = (okbits >> q) & 1u;
+        fu[q] = ok ? lu[q] : 0.0;
+        fv[q] = ok ? lv[q] : 0.0;
+        if (g.has_coarse) { fu[q] = dadd(fu[q], upu[q]); fv[q] = dadd(fv[q], upv[q]); }
+    }
+    if (g.vec_uv) {
+        *reinterpret_cast<double2*>(pu) = make_double2(fu[0], fu[1]);
+        *reinterpret_cast<double2*>(pv) = make_double2(fv[0], fv[1]);
+    } else {
+        pu[0] = fu[0]; pu[1] = fu[1]; pv[0] = fv[0]; pv[1] = fv[1];
+    }
+    if (M) {
+        unsigned char* pm = M + (size_t)y * a.mask_pitch + xb;
+        pm[0] = (unsigned char)(okbits & 1u);
+        pm[1] = (unsigned char)((okbits >> 1) & 1u);
+    }
+    if (a.stats) {
+        unsigned rc = 0;
+#pragma unroll
+        for (int q = 0; q < 2; ++q) {
+            // val = sqrt(u^2 + v^2); !(val < mag_thresh)  <=>  !(u^2 + v^2 < mag2)
+            const double s2 = dadd(dmul(fu[q], fu[q]), dmul(fv[q], fv[q]));
+            if (!(s2 < mag2)) { st.x += (unsigned)(xb + q); rc += 1u; }
+        }
+        st.c += rc;
+        st.y += (unsigned long long)rc * (unsigned)y;
+    }
+}
+
 template <int R>
 __device__ __forceinline__ void phase_solve(const LevelArgs& a, const PGeo& g, double* __restrict__ U,
                                             double* __restrict__ V, unsigned char* __restrict__ M, int m0,
@@ -430,7 +528,7 @@ __device__ __forceinline__ void phase_solve(const LevelArgs& a, const PGeo& g, d
 {
     using C = PhaseCfg<R>;
     constexpr int NPAIR = C::OUT_COLS / 2;                   // task = (row, pair of columns)
-    const int W = g.W, H = g.H;
+    const int W = g.W;
     const double det_eps = a.det_eps, mag2 = a.mag2_thresh;
     for (int t = t_begin; t < t_end; t += nthr) {
         const int ir = t / NPAIR;
@@ -438,78 +536,135 @@ __device__ __forceinline__ void phase_solve(const LevelArgs& a, const PGeo& g, d
         const int i = i_lo + ir;
         const int xb = g.xo0 + 2 * pr;                       // even; W even: both columns exist or none
         if (xb >= W) continue;
-        const double* sp0 = s_prod + 2 * (pr >> 1) + C::PHALF * (pr & 1);
+        const double* sp = s_prod + 2 * (pr >> 1) + C::PHALF * (pr & 1) + i * (5 * C::PPITCH);
         const int y = g.y0 + m0 + i;
-        double* pu = U + (size_t)y * a.uv_pitch + xb;
-        double* pv = V + (size_t)y * a.uv_pitch + xb;
-        double upu[2] = {0.0, 0.0}, upv[2] = {0.0, 0.0};
-        if (g.has_coarse) {                                  // parked by P1 (same CTA, barriers between)
-            if (g.vec_uv) {
-                const double2 u0 = *reinterpret_cast<const double2*>(pu), v0 = *reinterpret_cast<const double2*>(pv);
-                upu[0] = u0.x; upu[1] = u0.y; upv[0] = v0.x; upv[1] = v0.y;
-            } else {
-                upu[0] = pu[0]; upu[1] = pu[1]; upv[0] = pv[0]; upv[1] = pv[1];
-            }
-        }
-        const double* sp = sp0 + i * (5 * C::PPITCH);
         const double2 sxx = lds2(sp), syy = lds2(sp + C::PPITCH), sxy = lds2(sp + 2 * C::PPITCH);
         const double2 sxt = lds2(sp + 3 * C::PPITCH), syt = lds2(sp + 4 * C::PPITCH);
-        const bool yin = y >= R && y <= H - 1 - R;
-        double lu[2], lv[2], nus[2], nvs[2], dets[2];
-        unsigned okbits = 0;
-        bool fast = true;
+        solve_pair<R>(a, g, U, V, M, y, xb, sxx, syy, sxy, sxt, syt, det_eps, mag2, st);
+    }
+}
+
+// ------------------------------------------------------------------------------ R = 1: P2, P4
+// P2 for R = 1: one warp per product row (lane = 4 columns): gradients and the five raw
+// products of all 128 strip columns into the product ring (slot n0 + i).
+__device__ __forceinline__ void phase_products1(const PGeo& g, int vy0, int sb, int n0, const double* s_ab,
+                                                double* s_prod)
+{
+    using C = PhaseCfg<1>;
+    const int W = g.W, H = g.H;
+    const int lane = threadIdx.x & 31;
+    const int xb = g.c0 + 4 * lane;
+    for (int i = threadIdx.x >> 5; i < C::WIN; i += PH_NW) {
+        const int vy = vy0 + i;
+        int slot = n0 + i;
+        if (slot >= C::PR_ROWS) slot -= C::PR_ROWS;
+        double* d = s_prod + slot * (5 * AB_PITCH) + 2 * lane;
+        if ((unsigned)vy >= (unsigned)H) {                   // warp-uniform
+            const double z[4] = {0.0, 0.0, 0.0, 0.0};
 #pragma unroll
-        for (int q = 0; q < 2; ++q) {
-            const int x = xb + q;
-            const bool interior = yin && x >= R && x <= W - 1 - R;
-            const double xx = q ? sxx.y : sxx.x, yy = q ? syy.y : syy.x, xy = q ? sxy.y : sxy.x;
-            const double xt = q ? sxt.y : sxt.x, yt = q ? syt.y : syt.x;
-            dets[q] = dsub(dmul(xx, yy), dmul(xy, xy));
-            nus[q] = dsub(dmul(xy, yt), dmul(yy, xt));
-            nvs[q] = dsub(dmul(xt, xy), dmul(xx, yt));
-            const bool ok = interior && fabs(dets[q]) > det_eps;
-            okbits |= ok ? (1u << q) : 0u;
-            fast = (div2_fast(nus[q], nvs[q], dets[q], lu[q], lv[q]) || !ok) && fast;
+            for (int c = 0; c < 5; ++c) st4s(d + c * AB_PITCH, AB_HALF, z);
+            continue;
         }
-        if (!fast) {                                         // rare: exponent range outside the fast path
+        int s1 = sb + i + 1, s0 = sb + i;
+        if (s1 >= C::AB_ROWS) s1 -= C::AB_ROWS;
+        if (s0 >= C::AB_ROWS) s0 -= C::AB_ROWS;
+        const double* up = s_ab + s0 * (2 * AB_PITCH) + 2 * lane;
+        const double* cr = s_ab + s1 * (2 * AB_PITCH) + 2 * lane;
+        double pA[4], pB[4], cA[4], cB[4];
+        ld4s(up, AB_HALF, pA);
+        ld4s(up + AB_PITCH, AB_HALF, pB);
+        ld4s(cr, AB_HALF, cA);
+        ld4s(cr + AB_PITCH, AB_HALF, cB);
+        double pLA = up[AB_HALF - 1], pLB = up[AB_PITCH + AB_HALF - 1];
+        double cLA = cr[AB_HALF - 1], cLB = cr[AB_PITCH + AB_HALF - 1];
+        if (xb == 0) {                                       // reflect-101 at the left image border
+            pLA = pA[1]; pLB = pB[1]; cLA = cA[1]; cLB = cB[1];
+        }
+        double fx[4], fy[4], ft[4];
 #pragma unroll
-            for (int q = 0; q < 2; ++q) {
-                if ((okbits >> q) & 1u) {
-                    lu[q] = ddiv_slow(nus[q], dets[q]);
-                    lv[q] = ddiv_slow(nvs[q], dets[q]);
+        for (int q = 0; q < 4; ++q) {
+            const double a00 = q ? pA[q - 1] : pLA, a01 = pA[q];
+            const double a10 = q ? cA[q - 1] : cLA, a11 = cA[q];
+            const double b00 = q ? pB[q - 1] : pLB, b01 = pB[q];
+            const double b10 = q ? cB[q - 1] : cLB, b11 = cB[q];
+            // filter2D accumulation order ((k00 p00 + k01 p01) + k10 p10) + k11 p11 (:44-84)
+            const double fxa = dadd(dsub(dsub(a01, a00), a10), a11);
+            const double fxb = dadd(dsub(dsub(b01, b00), b10), b11);
+            const double sa = dadd(a00, a01), sbb = dadd(b00, b01);
+            const double fya = dadd(dsub(a10, sa), a11);
+            const double fyb = dadd(dsub(b10, sbb), b11);
+            const double fta = -dadd(dadd(sa, a10), a11);
+            const double ftb = dadd(dadd(sbb, b10), b11);
+            fx[q] = dadd(fxa, fxb);
+            fy[q] = dadd(fya, fyb);
+            ft[q] = dadd(fta, ftb);
+        }
+        if (g.edge) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const bool in = (unsigned)(xb + q) < (unsigned)W;
+                fx[q] = in ? fx[q] : 0.0;
+                fy[q] = in ? fy[q] : 0.0;
+                ft[q] = in ? ft[q] : 0.0;
+            }
+        }
+#pragma unroll
+        for (int c = 0; c < 5; ++c) {
+            double x[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+                x[q] = dmul(c == 1 || c == 4 ? fy[q] : fx[q], c == 0 ? fx[q] : (c == 1 || c == 2 ? fy[q] : ft[q]));
+            st4s(d + c * AB_PITCH, AB_HALF, x);
+        }
+    }
+}
+
+// P4 for R = 1: the calling warp owns output row y (window rows in ring slots r0, r1, r2), lane
+// l < OUT_LANES the four output columns xo0 + 4 l ..; 3x3 sums in get_Sum9's order (:122-157:
+// row-major, starting from 0.0), then the solve of both column pairs.
+__device__ __forceinline__ void phase_solve1(const LevelArgs& a, const PGeo& g, double* __restrict__ U,
+                                             double* __restrict__ V, unsigned char* __restrict__ M, int y,
+                                             int r0, int r1, int r2, const double* s_prod, StatAcc& st)
+{
+    using C = PhaseCfg<1>;
+    const int lane = threadIdx.x & 31;
+    const int xb = g.xo0 + 4 * lane;
+    if (lane >= C::OUT_LANES || xb >= g.W) return;
+    const int L = lane + 1;                                  // lane that owns these columns in the strip rows
+    double S[5][4];
+#pragma unroll
+    for (int c = 0; c < 5; ++c) {
+        double m[3][6];
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            const double* row = s_prod + (k == 0 ? r0 : (k == 1 ? r1 : r2)) * (5 * AB_PITCH) + c * AB_PITCH + 2 * L;
+            const double2 lo = lds2(row), hi = lds2(row + AB_HALF);
+            m[k][0] = row[AB_HALF - 1];
+            m[k][1] = lo.x; m[k][2] = lo.y; m[k][3] = hi.x; m[k][4] = hi.y;
+            m[k][5] = row[2];
+        }
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            double s = 0.0;
+#pragma unroll
+            for (int k = 0; k < 3; ++k)
+#pragma unroll
+                for (int j = 0; j < 3; ++j) {
+                    // 0.0 + x == x unless x is -0.0, which a square never is
+                    if (k == 0 && j == 0 && c < 2) s = m[0][q];
+                    else s = dadd(s, m[k][q + j]);
                 }
-            }
+            S[c][q] = s;
         }
-        double fu[2], fv[2];
+    }
+    const double det_eps = a.det_eps, mag2 = a.mag2_thresh;
 #pragma unroll
-        for (int q = 0; q < 2; ++q) {
-            const bool ok = (okbits >> q) & 1u;
-            fu[q] = ok ? lu[q] : 0.0;
-            fv[q] = ok ? lv[q] : 0.0;
-            if (g.has_coarse) { fu[q] = dadd(fu[q], upu[q]); fv[q] = dadd(fv[q], upv[q]); }
-        }
-        if (g.vec_uv) {
-            *reinterpret_cast<double2*>(pu) = make_double2(fu[0], fu[1]);
-            *reinterpret_cast<double2*>(pv) = make_double2(fv[0], fv[1]);
-        } else {
-            pu[0] = fu[0]; pu[1] = fu[1]; pv[0] = fv[0]; pv[1] = fv[1];
-        }
-        if (M) {
-            unsigned char* pm = M + (size_t)y * a.mask_pitch + xb;
-            pm[0] = (unsigned char)(okbits & 1u);
-            pm[1] = (unsigned char)((okbits >> 1) & 1u);
-        }
-        if (a.stats) {
-            unsigned rc = 0;
-#pragma unroll
-            for (int q = 0; q < 2; ++q) {
-                // val = sqrt(u^2 + v^2); !(val < mag_thresh)  <=>  !(u^2 + v^2 < mag2)
-                const double s2 = dadd(dmul(fu[q], fu[q]), dmul(fv[q], fv[q]));
-                if (!(s2 < mag2)) { st.x += (unsigned)(xb + q); rc += 1u; }
-            }
-            st.c += rc;
-            st.y += (unsigned long long)rc * (unsigned)y;
-        }
+    for (int h = 0; h < 2; ++h) {
+        if (xb + 2 * h >= g.W) break;
+        solve_pair<1>(a, g, U, V, M, y, xb + 2 * h, make_double2(S[0][2 * h], S[0][2 * h + 1]),
+                      make_double2(S[1][2 * h], S[1][2 * h + 1]), make_double2(S[2][2 * h], S[2][2 * h + 1]),
+                      make_double2(S[3][2 * h], S[3][2 * h + 1]), make_double2(S[4][2 * h], S[4][2 * h + 1]), det_eps,
+                      mag2, st);
     }
 }
 
@@ -687,14 +842,130 @@ __global__ void __launch_bounds__(PH_NT, 1) lk_level_phase_kernel(LevelArgs a, i
     }
 }
 
+// ------------------------------------------------------------------------------ kernel, R = 1
+// Same strip march with WIN = 15 rows per step.  Schedule of a step (two block-wide barriers):
+//   beta : P2(s) raw products -> ring, with the loads of P0(s+1) in flight
+//   gamma: every warp warps its row of P1(s+1) and solves its output row of P4(s); odd warps
+//          solve first, so that the latency-bound gathers of one half overlap the FP64 work
+//          of the other.
+// Output row n - 2 (relative to y0) is produced when product row n = s WIN + i has arrived.
+__global__ void __launch_bounds__(PH_NT, 1) lk_level_phase1_kernel(LevelArgs a, int th)
+{
+    constexpr int R = 1;
+    using C = PhaseCfg<1>;
+    extern __shared__ __align__(16) double sm[];
+    double* s_prod = sm;
+    double* s_ab = s_prod + C::PROD_D;
+    double* s_hr = s_ab + C::AB_D;
+
+    PGeo g;
+    g.W = a.w;
+    g.H = a.h;
+    g.xo0 = blockIdx.x * C::OUT_COLS;
+    g.c0 = g.xo0 - 4 * C::HL;
+    g.y0 = blockIdx.y * th;
+    g.y1 = min(g.y0 + th, a.h);
+    g.has_coarse = a.cu != nullptr;
+    g.edge = g.c0 < 0 || g.c0 + PH_PC > a.w;
+    const int pair = blockIdx.z;
+    const int H = g.H;
+
+    const double* __restrict__ A = a.A + (size_t)pair * a.a_pair_stride;
+    const double* __restrict__ B = a.B + (size_t)pair * a.b_pair_stride;
+    const double* __restrict__ cu = g.has_coarse ? a.cu + (size_t)pair * a.c_pair_stride : nullptr;
+    const double* __restrict__ cv = g.has_coarse ? a.cv + (size_t)pair * a.c_pair_stride : nullptr;
+    double* U = a.u + (size_t)pair * a.uv_pair_stride;
+    double* V = a.v + (size_t)pair * a.uv_pair_stride;
+    unsigned char* M = a.mask ? a.mask + (size_t)pair * a.mask_pair_stride : nullptr;
+    g.vec_img = ((reinterpret_cast<uintptr_t>(A) | reinterpret_cast<uintptr_t>(B) | (a.img_pitch * 8)) & 15) == 0;
+    g.vec_uv = ((reinterpret_cast<uintptr_t>(U) | reinterpret_cast<uintptr_t>(V) | (a.uv_pitch * 8)) & 15) == 0;
+    g.vec_c = false;
+    StatAcc st = {0, 0, 0};
+
+    const int rows = g.y1 - g.y0;
+    const int n_steps = (rows + 2 * R + C::WIN - 1) / C::WIN;
+    const int warp = threadIdx.x >> 5;
+
+    struct Step { int vy0, r_lo, sb, ka, nk; bool any; };
+    auto step_geo = [&](int s) {
+        Step q;
+        q.vy0 = g.y0 - R + s * C::WIN;                 // product row of block row 0
+        q.r_lo = s == 0 ? 0 : 1;
+        q.sb = (s * C::WIN) % C::AB_ROWS;
+        const int vlo = q.vy0 + q.r_lo - 1, vhi = q.vy0 + C::WIN - 1;
+        int lo = max(vlo, 0), hi = min(vhi, H - 1);
+        if (vlo <= -1 && vhi >= -1) { lo = 0; hi = max(hi, min(1, H - 1)); }
+        q.ka = (lo >> 1) - 1;
+        q.nk = (hi >> 1) + 2 - q.ka;
+        q.any = lo <= hi && s < n_steps;
+        return q;
+    };
+    // rows of P1: warp w takes row w + 1; the last warp takes row 0, which only exists in the first step
+    const int my_row = warp < C::WIN ? warp + 1 : 0;
+    Step cur = step_geo(0);
+    cur.any = false;
+    int k_have = -1000;
+    for (int s = -1; s < n_steps; ++s) {
+        const Step nxt = step_geo(s + 1);
+        const int n0 = s >= 0 ? (s * C::WIN) % C::PR_ROWS : 0;
+        {
+            UpPre q;
+            const bool up = nxt.any && g.has_coarse;
+            const int k_from = max(nxt.ka, k_have + 1), n_new = nxt.ka + nxt.nk - k_from;
+            if (up) up_rows_issue<C::HR_ROWS>(a, g, cu, cv, k_from, n_new, q);
+            if (s >= 0) phase_products1(g, cur.vy0, cur.sb, n0, s_ab, s_prod);
+            if (up) {
+                up_rows_finish(a, g, cu, cv, k_from, n_new, q, s_hr);
+                k_have = nxt.ka + nxt.nk - 1;
+            }
+        }
+        __syncthreads();
+        const int r_mine = nxt.any && my_row >= nxt.r_lo ? my_row : C::WIN + 1;
+        // this warp's output row: product row n = s WIN + warp has arrived -> output row n - 2
+        const int n = s * C::WIN + warp;
+        const bool solve = s >= 0 && warp < C::WIN && n >= 2 && n - 2 < rows;
+        int r2 = n0 + warp;
+        if (r2 >= C::PR_ROWS) r2 -= C::PR_ROWS;
+        const int r1 = r2 == 0 ? C::PR_ROWS - 1 : r2 - 1;
+        const int r0 = r1 == 0 ? C::PR_ROWS - 1 : r1 - 1;
+        if (warp & 1) {
+            if (solve) phase_solve1(a, g, U, V, M, g.y0 + n - 2, r0, r1, r2, s_prod, st);
+            phase_remap<R>(a, g, A, B, U, V, nxt.vy0, r_mine, C::WIN + 1, nxt.sb, s_hr, s_ab);
+        } else {
+            phase_remap<R>(a, g, A, B, U, V, nxt.vy0, r_mine, C::WIN + 1, nxt.sb, s_hr, s_ab);
+            if (solve) phase_solve1(a, g, U, V, M, g.y0 + n - 2, r0, r1, r2, s_prod, st);
+        }
+        __syncthreads();
+        cur = nxt;
+    }
+
+    if (a.stats) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            st.x += __shfl_xor_sync(0xffffffffu, st.x, o);
+            st.y += __shfl_xor_sync(0xffffffffu, st.y, o);
+            st.c += __shfl_xor_sync(0xffffffffu, st.c, o);
+        }
+        if ((threadIdx.x & 31) == 0 && st.c != 0) {
+            atomicAdd(&a.stats[pair].sum_x, (double)st.x);
+            atomicAdd(&a.stats[pair].sum_y, (double)st.y);
+            atomicAdd(&a.stats[pair].count, (double)st.c);
+        }
+    }
+}
+
 template <int R>
 cudaError_t launch_phase(const LevelArgs& a, int n_pairs, cudaStream_t s, unsigned long long* launches)
 {
     using C = PhaseCfg<R>;
     static bool attr_done = false;
     if (!attr_done) {
-        cudaError_t e = cudaFuncSetAttribute(lk_level_phase_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             (int)C::SMEM_BYTES);
+        cudaError_t e;
+        if constexpr (R == 1)
+            e = cudaFuncSetAttribute(lk_level_phase1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM_BYTES);
+        else
+            e = cudaFuncSetAttribute(lk_level_phase_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)C::SMEM_BYTES);
         if (e != cudaSuccess) return e;
         attr_done = true;
     }
@@ -717,7 +988,8 @@ cudaError_t launch_phase(const LevelArgs& a, int n_pairs, cudaStream_t s, unsign
     }
     const int chunks = (a.h + th - 1) / th;
     dim3 grid(strips, chunks, n_pairs);
-    lk_level_phase_kernel<R><<<grid, PH_NT, C::SMEM_BYTES, s>>>(a, th);
+    if constexpr (R == 1) lk_level_phase1_kernel<<<grid, PH_NT, C::SMEM_BYTES, s>>>(a, th);
+    else lk_level_phase_kernel<R><<<grid, PH_NT, C::SMEM_BYTES, s>>>(a, th);
     if (launches) *launches += 1;
     return cudaGetLastError();
 }
@@ -736,6 +1008,7 @@ cudaError_t launch_lk_level_phase(const LevelArgs& a, int n_pairs, cudaStream_t 
     if ((unsigned long long)a.img_pitch * (unsigned long long)a.h >= (1ull << 31)) return cudaSuccess;
     *handled = true;
     switch (a.radius) {
+        case 1: return launch_phase<1>(a, n_pairs, s, launches);
         case 2: return launch_phase<2>(a, n_pairs, s, launches);
         case 3: return launch_phase<3>(a, n_pairs, s, launches);
         case 4: return launch_phase<4>(a, n_pairs, s, launches);
