@@ -89,12 +89,19 @@ struct PhaseCfg {
 // reference's row-major order, which is not separable, so there are no horizontal / vertical
 // passes.  A step is WIN = 15 rows (not the window length); raw products of all 128 strip
 // columns are kept in a ring of WIN + 2 rows laid out like the warped-frame rows.
+#ifndef PH1_WIN
+#define PH1_WIN 15
+#define PH1_CTAS 1
+#endif
 template <>
 struct PhaseCfg<1> {
     static constexpr int HL = 1;
     static constexpr int OUT_LANES = 30;
     static constexpr int OUT_COLS = 4 * OUT_LANES;
-    static constexpr int WIN = 15;                    // rows per step
+    static constexpr int WIN = PH1_WIN;               // rows per step
+    static constexpr int CTAS = PH1_CTAS;             // CTAs per SM
+    static constexpr int NT = 32 * (WIN + 1);         // one warp per row of P1 (+ the row above the first step)
+    static constexpr int UPK = ((WIN + 1) / 2 + 3) * PH_PC / NT + 1;
     static constexpr int AB_ROWS = WIN + 1;
     static constexpr int HR_ROWS = (WIN + 1) / 2 + 3;
     static constexpr int PR_ROWS = WIN + 2;           // product-row ring
@@ -140,12 +147,13 @@ __device__ __forceinline__ int ppos(int X) { return ((X & 2) ? AB_HALF : 0) + 2 
 // column j) -> fine columns 2j, 2j+1.  Columns outside the image hold 0.  Split in two so that
 // the global loads are in flight while the thread does other work: issue() starts the loads of
 // the thread's (at most UP_K) tasks, finish() forms the rows and stores them.
-constexpr int UP_K = 3;
-struct UpPre { double sm1[UP_K], s0[UP_K], s1[UP_K]; };
+template <int UP_K>
+struct UpPreT { double sm1[UP_K], s0[UP_K], s1[UP_K]; };
+using UpPre = UpPreT<3>;
 
-template <int HR_ROWS>
+template <int HR_ROWS, int PH_NT = 512, int UP_K = 3>
 __device__ __forceinline__ void up_rows_issue(const LevelArgs& a, const PGeo& g, const double* __restrict__ cu,
-                                              const double* __restrict__ cv, int ka, int nk, UpPre& q)
+                                              const double* __restrict__ cv, int ka, int nk, UpPreT<UP_K>& q)
 {
     static_assert(UP_K * PH_NT >= HR_ROWS * PH_PC && HR_ROWS <= HR_RING, "UP_K too small");
     const int wc = a.wc, hc = a.hc;
@@ -166,8 +174,9 @@ __device__ __forceinline__ void up_rows_issue(const LevelArgs& a, const PGeo& g,
     }
 }
 
+template <int PH_NT = 512, int UP_K = 3>
 __device__ __forceinline__ void up_rows_finish(const LevelArgs& a, const PGeo& g, const double* __restrict__ cu,
-                                               const double* __restrict__ cv, int ka, int nk, const UpPre& q,
+                                               const double* __restrict__ cv, int ka, int nk, const UpPreT<UP_K>& q,
                                                double* s_hr)
 {
     const int wc = a.wc, hc = a.hc;
@@ -222,7 +231,11 @@ __device__ __forceinline__ void phase_remap(const LevelArgs& a, const PGeo& g, c
         unsigned inm = 0;                                    // columns of this lane inside the image
 #pragma unroll
         for (int i = 0; i < 4; ++i) inm |= (unsigned)(x0 + 32 * i) < (unsigned)W ? (1u << i) : 0u;
+#ifdef PH_KNOCK_REMAP
+        if (false) {
+#else
         if (g.has_coarse) {
+#endif
             // vertical pass of cv::pyrUp from the rows of P0
             const int k = yy >> 1;
             const double* hm = s_hr + (((k + 1) & (HR_RING - 1)) * 2) * PH_PC + lane;   // row k-1, plane u
@@ -554,7 +567,7 @@ __device__ __forceinline__ void phase_products1(const PGeo& g, int vy0, int sb, 
     const int W = g.W, H = g.H;
     const int lane = threadIdx.x & 31;
     const int xb = g.c0 + 4 * lane;
-    for (int i = threadIdx.x >> 5; i < C::WIN; i += PH_NW) {
+    for (int i = threadIdx.x >> 5; i < C::WIN; i += C::NT / 32) {
         const int vy = vy0 + i;
         int slot = n0 + i;
         if (slot >= C::PR_ROWS) slot -= C::PR_ROWS;
@@ -620,17 +633,16 @@ __device__ __forceinline__ void phase_products1(const PGeo& g, int vy0, int sb, 
 }
 
 // P4 for R = 1: the calling warp owns output row y (window rows in ring slots r0, r1, r2), lane
-// l < OUT_LANES the four output columns xo0 + 4 l ..; 3x3 sums in get_Sum9's order (:122-157:
+// L (1 .. 30) the four output columns c0 + 4 L ..; 3x3 sums in get_Sum9's order (:122-157:
 // row-major, starting from 0.0), then the solve of both column pairs.
 __device__ __forceinline__ void phase_solve1(const LevelArgs& a, const PGeo& g, double* __restrict__ U,
                                              double* __restrict__ V, unsigned char* __restrict__ M, int y,
                                              int r0, int r1, int r2, const double* s_prod, StatAcc& st)
 {
     using C = PhaseCfg<1>;
-    const int lane = threadIdx.x & 31;
-    const int xb = g.xo0 + 4 * lane;
-    if (lane >= C::OUT_LANES || xb >= g.W) return;
-    const int L = lane + 1;                                  // lane that owns these columns in the strip rows
+    const int L = threadIdx.x & 31;                          // lane L holds strip columns 4L .. 4L+3
+    const int xb = g.c0 + 4 * L;
+    const bool active = L >= C::HL && L < 32 - C::HL && xb < g.W;
     double S[5][4];
 #pragma unroll
     for (int c = 0; c < 5; ++c) {
@@ -639,9 +651,10 @@ __device__ __forceinline__ void phase_solve1(const LevelArgs& a, const PGeo& g, 
         for (int k = 0; k < 3; ++k) {
             const double* row = s_prod + (k == 0 ? r0 : (k == 1 ? r1 : r2)) * (5 * AB_PITCH) + c * AB_PITCH + 2 * L;
             const double2 lo = lds2(row), hi = lds2(row + AB_HALF);
-            m[k][0] = row[AB_HALF - 1];
+            // columns 4L-1 and 4L+4 come from the neighbouring lanes (the halo lanes 0 and 31 only provide)
+            m[k][0] = __shfl_up_sync(0xffffffffu, hi.y, 1);
             m[k][1] = lo.x; m[k][2] = lo.y; m[k][3] = hi.x; m[k][4] = hi.y;
-            m[k][5] = row[2];
+            m[k][5] = __shfl_down_sync(0xffffffffu, lo.x, 1);
         }
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
@@ -658,6 +671,7 @@ __device__ __forceinline__ void phase_solve1(const LevelArgs& a, const PGeo& g, 
         }
     }
     const double det_eps = a.det_eps, mag2 = a.mag2_thresh;
+    if (!active) return;
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
         if (xb + 2 * h >= g.W) break;
@@ -849,7 +863,7 @@ __global__ void __launch_bounds__(PH_NT, 1) lk_level_phase_kernel(LevelArgs a, i
 //          solve first, so that the latency-bound gathers of one half overlap the FP64 work
 //          of the other.
 // Output row n - 2 (relative to y0) is produced when product row n = s WIN + i has arrived.
-__global__ void __launch_bounds__(PH_NT, 1) lk_level_phase1_kernel(LevelArgs a, int th)
+__global__ void __launch_bounds__(PhaseCfg<1>::NT, PhaseCfg<1>::CTAS) lk_level_phase1_kernel(LevelArgs a, int th)
 {
     constexpr int R = 1;
     using C = PhaseCfg<1>;
@@ -909,13 +923,13 @@ __global__ void __launch_bounds__(PH_NT, 1) lk_level_phase1_kernel(LevelArgs a, 
         const Step nxt = step_geo(s + 1);
         const int n0 = s >= 0 ? (s * C::WIN) % C::PR_ROWS : 0;
         {
-            UpPre q;
+            UpPreT<C::UPK> q;
             const bool up = nxt.any && g.has_coarse;
             const int k_from = max(nxt.ka, k_have + 1), n_new = nxt.ka + nxt.nk - k_from;
-            if (up) up_rows_issue<C::HR_ROWS>(a, g, cu, cv, k_from, n_new, q);
+            if (up) up_rows_issue<C::HR_ROWS, C::NT, C::UPK>(a, g, cu, cv, k_from, n_new, q);
             if (s >= 0) phase_products1(g, cur.vy0, cur.sb, n0, s_ab, s_prod);
             if (up) {
-                up_rows_finish(a, g, cu, cv, k_from, n_new, q, s_hr);
+                up_rows_finish<C::NT, C::UPK>(a, g, cu, cv, k_from, n_new, q, s_hr);
                 k_have = nxt.ka + nxt.nk - 1;
             }
         }
@@ -928,7 +942,10 @@ __global__ void __launch_bounds__(PH_NT, 1) lk_level_phase1_kernel(LevelArgs a, 
         if (r2 >= C::PR_ROWS) r2 -= C::PR_ROWS;
         const int r1 = r2 == 0 ? C::PR_ROWS - 1 : r2 - 1;
         const int r0 = r1 == 0 ? C::PR_ROWS - 1 : r1 - 1;
-        if (warp & 1) {
+#ifndef PH1_SOLVE_FIRST
+#define PH1_SOLVE_FIRST (warp < C::NT / 64)      // two solve-first and two remap-first warps per SM sub-partition
+#endif
+        if (PH1_SOLVE_FIRST) {
             if (solve) phase_solve1(a, g, U, V, M, g.y0 + n - 2, r0, r1, r2, s_prod, st);
             phase_remap<R>(a, g, A, B, U, V, nxt.vy0, r_mine, C::WIN + 1, nxt.sb, s_hr, s_ab);
         } else {
@@ -973,7 +990,9 @@ cudaError_t launch_phase(const LevelArgs& a, int n_pairs, cudaStream_t s, unsign
     // Chunk height: a multiple of the vertical block length, so that block boundaries sit at
     // the same absolute rows whatever the chunking (bit-identical results for any batch size).
     // Pick the height that minimises (waves of resident CTAs) x (steps a CTA runs).
-    const long resident = 148;
+    long resident = 148;
+    int nt = PH_NT;
+    if constexpr (R == 1) { resident = 148 * C::CTAS; nt = C::NT; }
     const int max_m = (a.h + C::WIN - 1) / C::WIN;
     long best_cost = -1;
     int th = C::WIN * max_m;
@@ -988,7 +1007,7 @@ cudaError_t launch_phase(const LevelArgs& a, int n_pairs, cudaStream_t s, unsign
     }
     const int chunks = (a.h + th - 1) / th;
     dim3 grid(strips, chunks, n_pairs);
-    if constexpr (R == 1) lk_level_phase1_kernel<<<grid, PH_NT, C::SMEM_BYTES, s>>>(a, th);
+    if constexpr (R == 1) lk_level_phase1_kernel<<<grid, nt, C::SMEM_BYTES, s>>>(a, th);
     else lk_level_phase_kernel<R><<<grid, PH_NT, C::SMEM_BYTES, s>>>(a, th);
     if (launches) *launches += 1;
     return cudaGetLastError();

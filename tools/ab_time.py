@@ -8,7 +8,7 @@ sys.path.insert(0, %r)
 import torch, importlib
 from of_b200_loader import ofb
 synth = importlib.import_module("optical_flow_b200.synth")
-h, w, L, r, n = 1080, 1920, 3, 7, 16
+h, w, L, r, n = 1080, 1920, 3, int(os.environ.get("AB_R", "7")), 16
 fr = torch.from_numpy(synth.synth_frames(n + 1, h, w, seed=1234)).cuda()
 U = torch.empty((n, h, w), dtype=torch.float64, device="cuda"); V = torch.empty_like(U)
 with ofb.Context(0, win_radius=r) as ctx:
