@@ -81,11 +81,18 @@ class ClockSampler:
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
-                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+                 "-lms", "20"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
+            t0 = time.time()                       # nvidia-smi needs ~0.1-0.5 s to deliver its first row
+            while not self.rows and time.time() - t0 < 3.0:
+                time.sleep(0.01)
         except Exception:
             self.proc = None
+
+    def mark(self):
+        """Start of the timed region: drop what was sampled before it."""
+        self.rows = []
 
     def _read(self):
         for line in self.proc.stdout:
@@ -94,7 +101,6 @@ class ClockSampler:
     def stop(self):
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
         self.proc.terminate()
         try:
             self.proc.wait(timeout=2)
@@ -228,8 +234,9 @@ def run_ours(args):
     launches0 = ctx.launch_count
     e0 = torch.cuda.Event(enable_timing=True)
     e1 = torch.cuda.Event(enable_timing=True)
-    barrier()
     sampler.start()
+    barrier()
+    sampler.mark()
     e0.record()
     for i in range(args.steps):
         step()
@@ -309,8 +316,33 @@ def run_ours(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_u8_val = world * n8 * u8_steps / float(t.item())
 
+    # ---- the reference's own window (3x3, r = 1; bit-exact path), device-resident like `value` ---
+    r1 = None
+    if radius != 1:
+        with ofb.Context(local_rank, win_radius=1) as c1:
+            for _ in range(3):
+                c1.flow_batch_dev(frames, LEVELS, U, V, S)
+            barrier()
+            c1.set_timing(True)
+            r1_steps = max(2, min(args.steps, 20))
+            e0.record()
+            for _ in range(r1_steps):
+                c1.flow_batch_dev(frames, LEVELS, U, V, S)
+            e1.record()
+            barrier()
+            l0s = [ms for kind, level, ms in c1.get_timing() if kind == 1 and level == 0]
+            t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+            if world > 1:
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            r1 = {"value": world * pairs * r1_steps / (float(t.item()) * 1e-3), "unit": UNIT, "steps": r1_steps,
+                  "level0_launch_ms": sum(l0s) / len(l0s) if l0s else None,
+                  "note": "same workload with the reference's own 3x3 window (get_Sum9), bit-exact kernel"}
+
     if rank == 0:
         peak, peak_src = measured_peaks()
+        if r1 and r1["level0_launch_ms"]:
+            r1["level0_frac"] = level0_bytes_per_pair(W, H, LEVELS) * pairs / (r1["level0_launch_ms"] * 1e-3) / 1e9 / peak
+            r1["whole_path_frac"] = algorithmic_bytes_per_pair(W, H, LEVELS) * (r1["value"] / world) / (peak * 1e9)
         l0 = sum(lvl0_ms) / len(lvl0_ms) if lvl0_ms else None
         roof = None
         if l0:
@@ -355,6 +387,7 @@ def run_ours(args):
                                   "d2h_bytes_per_step": 32 * n8, "pairs_per_call": n8,
                                   "api": "of_ctf_u8_stream: 8-bit frames in (the synthetic stream quantised to 8 bits), "
                                          "converted on the device, gesture statistics per pair out"},
+            "window_3x3": r1,
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": roof,
@@ -369,7 +402,7 @@ def run_ours(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=300)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--pairs", type=int, default=PAIRS)
