@@ -210,6 +210,15 @@ OF_API of_status of_ctx_set_timing(of_ctx *ctx, int enable);
 OF_API of_status of_ctx_get_timing(of_ctx *ctx, int max_entries, int *kinds, int *levels,
                                    float *ms, int *n);
 
+/* Parity triage: copies one plane of pyramid level `level` >= 1 as left in the
+ * context by the most recent pyramid call: the Gaussian pyramid image of frame 1 / frame 2 of
+ * pair `pair` (getGaussianPyramid :566-575; unwarped -- warped levels never exist in memory) or
+ * the accumulated flow u_l / v_l of that level (tmpu / tmpv after :634-637).  dst may be a host
+ * or a device pointer; dst = NULL only reports the level's size.  Waits for that call. */
+enum { OF_LEVEL_FRAME1 = 0, OF_LEVEL_FRAME2 = 1, OF_LEVEL_FLOW_U = 2, OF_LEVEL_FLOW_V = 3 };
+OF_API of_status of_ctx_get_level_f64(of_ctx *ctx, int what, int level, int pair, double *dst,
+                                      size_t dst_step_bytes, int *width, int *height);
+
 /* Number of kernel launches issued through this context since creation (bench evidence). */
 OF_API unsigned long long of_ctx_launch_count(const of_ctx *ctx);
 

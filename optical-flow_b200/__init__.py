@@ -30,6 +30,7 @@ EXPORTS = (
     "of_ctf_f64_batch_dev", "of_gesture_stats_dev", "of_pyr_down_f64_dev",
     "of_ctx_synchronize", "of_ctx_launch_count", "of_ctx_set_timing", "of_ctx_get_timing",
     "of_bgr2gray_u8_dev", "of_live_diff_f64_dev", "of_live_diff_f64", "of_ctf_u8_stream",
+    "of_ctx_get_level_f64",
 )
 
 
@@ -94,6 +95,7 @@ def lib():
                                        vp, sz, sz, vp, vp]
     L.of_gesture_stats_dev.argtypes = [vp, ci, vp, vp, sz, ci, ci, sz, vp, vp]
     L.of_pyr_down_f64_dev.argtypes = [vp, vp, ci, ci, sz, vp, sz, vp]
+    L.of_ctx_get_level_f64.argtypes = [vp, ci, ci, ci, vp, sz, C.POINTER(ci), C.POINTER(ci)]
     L.of_bgr2gray_u8_dev.argtypes = [vp, vp, ci, ci, sz, vp, sz, ci, vp]
     L.of_live_diff_f64_dev.argtypes = [vp, vp, vp, ci, ci, sz, dbl, ci, ci, vp, sz, vp]
     L.of_live_diff_f64.argtypes = [vp, vp, vp, ci, ci, ci, sz, ci, dbl, ci, ci, vp, sz]
@@ -202,6 +204,17 @@ class Context:
 
     def set_timing(self, enable: bool):
         self._check(lib().of_ctx_set_timing(self._h, int(bool(enable))))
+
+    def get_level(self, what: str, level: int, pair: int = 0):
+        """Parity triage: plane ``what`` ('frame1', 'frame2', 'u', 'v') of pyramid level ``level`` >= 1
+        of pair ``pair`` as left by the most recent pyramid call (numpy array)."""
+        code = {"frame1": 0, "frame2": 1, "u": 2, "v": 3}[what]
+        w, h = C.c_int(0), C.c_int(0)
+        self._check(lib().of_ctx_get_level_f64(self._h, code, int(level), int(pair), None, 0, C.byref(w), C.byref(h)))
+        out = np.empty((h.value, w.value), np.float64)
+        self._check(lib().of_ctx_get_level_f64(self._h, code, int(level), int(pair), out.ctypes.data_as(C.c_void_p),
+                                               out.strides[0], C.byref(w), C.byref(h)))
+        return out
 
     def get_timing(self):
         """[(kind, level, ms)] of every launch since set_timing(True) (at most 8192);

@@ -4,6 +4,7 @@
 //
 // There is no CPU path in this file: every entry point either launches the CUDA kernels
 // or returns an error code.
+#include <nvtx3/nvToolsExt.h>
 #include <cuda_runtime.h>
 
 #include <cmath>
@@ -60,6 +61,12 @@ struct of_ctx {
     std::vector<cudaEvent_t> tev;      // 2 events per timed launch
     std::vector<int> tkind, tlevel;
     size_t tcount = 0;
+    // geometry of the most recent batch call (of_ctx_get_level_f64, parity triage)
+    struct LastLevel { int w, h; size_t pitch, img_stride, pyr_off, flow_u_off, flow_v_off; };
+    std::vector<LastLevel> last;
+    int last_pairs = 0;
+    bool last_shared = false;
+    cudaStream_t last_stream = nullptr;
 };
 
 namespace {
@@ -192,6 +199,11 @@ struct TimedLaunch {
     bool on;
     TimedLaunch(of_ctx* c, cudaStream_t st, int kind, int level) : ctx(c), s(st), on(c->timing)
     {
+        // NVTX range per stage (the reference's per-stage timers, serial.cpp:204,261,303,320): free
+        // when no profiler is attached
+        char name[40];
+        snprintf(name, sizeof name, kind == 0 ? "of_b200 pyrDown -> L%d" : "of_b200 lk_level L%d", level);
+        nvtxRangePushA(name);
         if (!on) return;
         if (ctx->tcount >= 8192) { on = false; return; }
         if (ctx->tev.size() < 2 * (ctx->tcount + 1)) {
@@ -208,6 +220,7 @@ struct TimedLaunch {
     }
     ~TimedLaunch()
     {
+        nvtxRangePop();
         if (!on) return;
         cudaEventRecord(ctx->tev[2 * ctx->tcount + 1], s);
         ctx->tcount += 1;
@@ -259,6 +272,13 @@ of_status run_batch(of_ctx* ctx, int n_pairs, const double* img1, const double* 
     char* base = ctx->scratch.base;
     const size_t in_pitch = step / sizeof(double);
     const size_t in_stride = img_pair_stride / sizeof(double);
+    ctx->last.assign(L, of_ctx::LastLevel{});
+    for (int l = 0; l < L; ++l)
+        ctx->last[l] = {p.g[l].w, p.g[l].h, p.g[l].pitch, p.g[l].img_stride, l ? p.pyr_off[l] : 0,
+                        l ? p.flow_u_off[l] : 0, l ? p.flow_v_off[l] : 0};
+    ctx->last_pairs = n_pairs;
+    ctx->last_shared = shared;
+    ctx->last_stream = s;
 
     // ---- Gaussian pyramids (getGaussianPyramid :566-575, both frames :587-597) ------------
     for (int l = 1; l < L; ++l) {
@@ -480,6 +500,36 @@ of_status of_ctx_get_timing(of_ctx* ctx, int max_entries, int* kinds, int* level
         levels[cnt] = ctx->tlevel[i];
     }
     *n = cnt;
+    return OF_OK;
+}
+
+of_status of_ctx_get_level_f64(of_ctx* ctx, int what, int level, int pair, double* dst,
+                               size_t dst_step_bytes, int* width, int* height)
+{
+    if (!ctx) return OF_E_BADARG;
+    if (ctx->last.empty()) return fail(ctx, OF_E_BADARG, "no pyramid call has run on this context yet");
+    if (level < 1 || level >= (int)ctx->last.size())
+        return fail(ctx, OF_E_BADARG, "level %d: only levels 1..%d live in the context (level 0 is the caller's)", level,
+                    (int)ctx->last.size() - 1);
+    if (pair < 0 || pair >= ctx->last_pairs) return fail(ctx, OF_E_BADARG, "pair %d out of range", pair);
+    if (what < OF_LEVEL_FRAME1 || what > OF_LEVEL_FLOW_V) return fail(ctx, OF_E_BADARG, "unknown plane %d", what);
+    const of_ctx::LastLevel& g = ctx->last[level];
+    if (width) *width = g.w;
+    if (height) *height = g.h;
+    if (!dst) return OF_OK;                                  // size query
+    if (dst_step_bytes < (size_t)g.w * sizeof(double)) return fail(ctx, OF_E_BADARG, "dst_step_bytes too small");
+    const char* base = ctx->scratch.base;
+    const double* src;
+    if (what == OF_LEVEL_FRAME1)
+        src = (const double*)(base + g.pyr_off) + g.img_stride * pair;
+    else if (what == OF_LEVEL_FRAME2)
+        src = (const double*)(base + g.pyr_off) + g.img_stride * (ctx->last_shared ? pair + 1 : ctx->last_pairs + pair);
+    else
+        src = (const double*)(base + (what == OF_LEVEL_FLOW_U ? g.flow_u_off : g.flow_v_off)) + g.img_stride * pair;
+    OF_CUDA(ctx, cudaSetDevice(ctx->device));
+    OF_CUDA(ctx, cudaStreamSynchronize(ctx->last_stream));
+    OF_CUDA(ctx, cudaMemcpy2D(dst, dst_step_bytes, src, g.pitch * sizeof(double), (size_t)g.w * sizeof(double), g.h,
+                              cudaMemcpyDefault));
     return OF_OK;
 }
 

@@ -188,6 +188,30 @@ def test_pyr_down_primitive(ofb, c_oracle, torch_cuda):
             assert np.array_equal(dst.cpu().numpy(), c_oracle.pyr_down(x)), (h, w)
 
 
+def test_per_level_triage_planes(ofb, table_pair):
+    """of_ctx_get_level_f64: the pyramid levels and the accumulated flow of every
+    level match the oracle's trace bit for bit at r = 1 (the reference's window)."""
+    from oracle import lk_oracle as O
+    a, b = table_pair
+    a, b = a[:256, :320].copy(), b[:256, :320].copy()
+    tr = {}
+    O.coarse_to_fine(a, b, 4, trace=tr)
+    pa, pb = O.gaussian_pyramid(a, 4), O.gaussian_pyramid(b, 4)
+    with ofb.Context(0) as ctx:
+        with pytest.raises(ofb.BadArgError):
+            ctx.get_level("u", 1)                       # nothing has run yet
+        ctx.coarseToFineEstimation(a, b, 4)
+        for lvl in (1, 2, 3):
+            assert np.array_equal(ctx.get_level("frame1", lvl), pa[lvl]), lvl
+            assert np.array_equal(ctx.get_level("frame2", lvl), pb[lvl]), lvl
+            assert np.array_equal(ctx.get_level("u", lvl), tr[("u", lvl)]), lvl
+            assert np.array_equal(ctx.get_level("v", lvl), tr[("v", lvl)]), lvl
+        with pytest.raises(ofb.BadArgError):
+            ctx.get_level("u", 0)                       # level 0 is the caller's output
+        with pytest.raises(ofb.BadArgError):
+            ctx.get_level("u", 4)
+
+
 # ------------------------------------------------------------------ errors
 def test_error_codes(ofb):
     z = np.zeros((30, 40))

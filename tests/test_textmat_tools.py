@@ -63,6 +63,28 @@ def test_of_pair_cli_reproduces_kat1(tmp_path, table_pair, kat_golden):
 
 
 @pytest.mark.gpu
+def test_of_pair_cli_timing_json_and_level_dump(tmp_path, table_pair):
+    """per-stage device timings as JSON and per-level triage planes."""
+    a, b = table_pair
+    np.save(tmp_path / "a.npy", a[:256, :320])
+    np.save(tmp_path / "b.npy", b[:256, :320])
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "of_pair.py"), str(tmp_path / "a.npy"),
+                        str(tmp_path / "b.npy"), "--levels", "3", "--format", "npy", "--out", str(tmp_path / "o"),
+                        "--timing-json", str(tmp_path / "t.json"), "--dump-levels", str(tmp_path / "lv")],
+                       capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    t = json.load(open(tmp_path / "t.json"))
+    assert [(x["stage"], x["level"]) for x in t["stages"]] == [
+        ("pyrDown", 1), ("pyrDown", 1), ("pyrDown", 2), ("lk_level", 2), ("lk_level", 1), ("lk_level", 0)]
+    assert all(x["ms"] > 0 for x in t["stages"])
+    from oracle import lk_oracle as O
+    pa = O.gaussian_pyramid(a[:256, :320], 3)
+    for l in (1, 2):
+        assert np.array_equal(np.load(tmp_path / ("lv_L%d_frame1.npy" % l)), pa[l])
+        assert np.load(tmp_path / ("lv_L%d_u.npy" % l)).shape == pa[l].shape
+
+
+@pytest.mark.gpu
 def test_of_video_cli_stats(tmp_path, c_oracle):
     synth = importlib.import_module("optical_flow_b200.synth")
     fr = synth.synth_frames(4, 96, 128, seed=3, gesture=True) * 40.0

@@ -50,6 +50,10 @@ def main(argv=None):
     ap.add_argument("--check-u")
     ap.add_argument("--check-v")
     ap.add_argument("--device", type=int, default=0)
+    ap.add_argument("--timing-json", help="write the device time of every stage (pyrDown / fused level kernel per "
+                                          "pyramid level) as JSON, like the reference's per-stage timers")
+    ap.add_argument("--dump-levels", metavar="STEM", help="parity triage: save the pyramid images and the accumulated "
+                                                          "flow of every level >= 1 as <STEM>_L<l>_<plane>.npy")
     a = ap.parse_args(argv)
 
     i1, i2 = read_gray(a.img1), read_gray(a.img2)
@@ -60,7 +64,20 @@ def main(argv=None):
     levels = 1 if a.single else (a.levels or ofb.getMaxLayer(i1))
     print("%d, %d, Max layer = %d" % (i1.shape[0], i1.shape[1], levels))       # the harness's first line
     with ofb.Context(a.device, win_radius=a.radius) as ctx:
+        if a.timing_json:
+            ctx.set_timing(True)
         u, v = ctx.getLucasKanadeOpticalFlow(i1, i2) if a.single else ctx.coarseToFineEstimation(i1, i2, levels)
+        if a.timing_json:
+            import json
+            stages = [{"stage": "pyrDown" if k == 0 else "lk_level", "level": l, "ms": ms} for k, l, ms in ctx.get_timing()]
+            json.dump({"width": int(i1.shape[1]), "height": int(i1.shape[0]), "levels": levels, "win_radius": a.radius,
+                       "stages": stages, "device_ms_total": sum(x["ms"] for x in stages)}, open(a.timing_json, "w"), indent=1)
+            print("wrote", a.timing_json)
+        if a.dump_levels and not a.single:
+            for l in range(1, levels):
+                for plane in ("frame1", "frame2", "u", "v"):
+                    np.save("%s_L%d_%s.npy" % (a.dump_levels, l, plane), ctx.get_level(plane, l))
+            print("wrote %s_L*_*.npy" % a.dump_levels)
     if a.format == "txt":
         print("wrote", textmat.save_mat(u, a.out + "_u"), textmat.save_mat(v, a.out + "_v"))
     else:
