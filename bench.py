@@ -125,6 +125,16 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
+_emit = print
+
+
+def host_threads():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
 def synth(n_frames, seed=1234):
     import importlib
     from of_b200_loader import ofb  # noqa: F401
@@ -136,7 +146,7 @@ def cpu_baseline_run(frames, n_pairs, repeats=1):
     all host threads.  Returns (pairs_per_s, cores, seconds)."""
     from oracle import c_oracle as CO
     CO.build()
-    cores = os.cpu_count() or 1
+    cores = CO.set_threads(host_threads())
     CO.coarse_to_fine(frames[0][:64, :64].copy(), frames[1][:64, :64].copy(), 1, 1)   # thread-pool warm-up
     t0 = time.perf_counter()
     done = 0
@@ -160,7 +170,7 @@ def run_reference(args):
     frames = synth(sample + 1)
     from oracle import c_oracle as CO
     CO.build()
-    cores = os.cpu_count() or 1
+    cores = CO.set_threads(host_threads())      # torchrun exports OMP_NUM_THREADS=1: use every host thread anyway
     for _ in range(max(args.warmup, 1)):
         CO.coarse_to_fine(frames[0], frames[1], LEVELS, RADIUS)
     t0 = time.perf_counter()
@@ -182,7 +192,7 @@ def run_reference(args):
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    _emit(json.dumps(line))
 
 
 def run_ours(args):
@@ -246,7 +256,9 @@ def run_ours(args):
     ms_total = e0.elapsed_time(e1)
     # per-launch durations of every kernel launched inside the timed region (events on the
     # launching stream, recorded by the library around each launch)
+    per_kernel = {}
     for kind, level, ms in ctx.get_timing():
+        per_kernel.setdefault((kind, level), []).append(ms)
         if kind == 1 and level == 0:
             lvl0_ms.append(ms)
         elif kind == 1:
@@ -360,10 +372,35 @@ def run_ours(args):
                     "whole_path_frac": algorithmic_bytes_per_pair(W, H, LEVELS) * (value / world) / (peak * 1e9),
                     "kernel_ms_per_step": {"level0": l0, "coarser_levels": sum(lvl_ms) / args.steps,
                                            "pyr_down": sum(pyr_ms) / args.steps}}
+        if roof:
+            # bytes-per-pixel roofline of every kernel of the step: fused level kernel of level l
+            # 32 B per level-l pixel (+ 16 B per coarser pixel), pyrDown producing level l 8 B read per source
+            # pixel + 8 B written per destination pixel, per frame
+            n = level_sizes(W, H, LEVELS)
+            table = []
+            for (kind, level), v in sorted(per_kernel.items()):
+                ms_launch = sum(v) / len(v)
+                launches_per_step = len(v) / args.steps
+                if kind == 1:
+                    b = (32 * n[level] + (16 * n[level + 1] if level < LEVELS - 1 else 0)) * pairs
+                    name = "lk_level L%d" % level
+                else:
+                    b = 8 * (n[level - 1] + n[level]) * (pairs + 1) / launches_per_step
+                    name = "pyrDown -> L%d" % level
+                gbs = b / (ms_launch * 1e-3) / 1e9
+                table.append({"kernel": name, "launch_ms": ms_launch, "launches_per_step": launches_per_step,
+                              "algorithmic_bytes_per_launch": int(b), "achieved_gbs": gbs, "frac": gbs / peak})
+            roof["per_kernel"] = table
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
             v, cores, secs = cpu_baseline_run(frames_h, 64)
-            cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
+            from oracle import c_oracle as CO
+            CO.set_threads(8)                  # the reference's hard-coded team size (ParallelVideoPyr.cpp:164)
+            t0 = time.perf_counter()
+            for k in range(8):
+                CO.coarse_to_fine(frames_h[k], frames_h[k + 1], LEVELS, RADIUS)
+            v8 = 8 / (time.perf_counter() - t0)
+            cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "value_8_threads": v8,
                    "sample": "64 pairs (the first 16 consecutive pairs of the same synthetic 1080p stream, L=3, r=%d, "
                              "four times over), oracle/lk_oracle.c C+OpenMP port of the reference path, all host "
                              "threads, %.1f s" % (RADIUS, secs)}
@@ -393,7 +430,7 @@ def run_ours(args):
             "roofline": roof,
             "cpu_baseline": cpu,
         }
-        print(json.dumps(line), flush=True)
+        _emit(json.dumps(line))
     ctx.close()
     if world > 1:
         dist.destroy_process_group()
@@ -409,6 +446,16 @@ def main():
     ap.add_argument("--radius", type=int, default=RADIUS)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
+    # torchrun exports OMP_NUM_THREADS=1; the CPU legs (reference arm, cpu_baseline) are to use every
+    # host thread, and libgomp reads the variable when it is loaded, so set it before anything imports it
+    os.environ["OMP_NUM_THREADS"] = str(host_threads())
+    # stdout carries exactly one JSON line: anything a library prints there (NCCL's version banner, ...)
+    # goes to stderr instead
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    global _emit
+    _emit = lambda text: os.write(real_stdout, (text + "\n").encode())
     if args.impl == "reference":
         run_reference(args)
     else:

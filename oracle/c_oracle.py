@@ -43,6 +43,17 @@ def lib():
     return _lib
 
 
+def set_threads(n: int) -> int:
+    """OpenMP team size of the port (the reference hard-codes 8, ParallelVideoPyr.cpp:164; the CPU
+    baseline uses every host thread).  torchrun exports OMP_NUM_THREADS=1, so the bench sets it
+    explicitly.  Returns the value in effect."""
+    lib()
+    g = C.CDLL("libgomp.so.1")
+    g.omp_set_num_threads(int(n))
+    g.omp_get_max_threads.restype = C.c_int
+    return int(g.omp_get_max_threads())
+
+
 def _p(a):
     return a.ctypes.data_as(C.POINTER(C.c_double))
 
