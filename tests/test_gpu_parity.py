@@ -65,6 +65,8 @@ def test_kat7_pyramid(ofb, table_pair, kat_golden, c_oracle):
 SHAPES = [  # (H, W, L)
     (448, 640, 3), (37, 53, 1), (2, 2, 1), (1, 9, 1), (9, 1, 1), (2, 16, 2), (16, 2, 2),
     (64, 96, 3), (120, 200, 4), (96, 96, 6), (33, 300, 1), (300, 34, 2), (8, 8, 4),
+    # around the strip widths of the fused kernels (120 output columns at r = 1, 112 at r = 7)
+    (47, 122, 1), (62, 242, 2), (200, 118, 1), (46, 226, 2),
 ]
 
 
