@@ -296,7 +296,11 @@ __device__ __forceinline__ void phase_remap(const LevelArgs& a, const PGeo& g, c
                 double sv[4][4];                             // 16 gathers, issued back to back
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
+#ifdef PH_KNOCK_L1
+                    const double* pa = F + ((unsigned)tp[i].off & 1023u);
+#else
                     const double* pa = F + (unsigned)tp[i].off;     // off >= 0: one IMAD.WIDE.U32
+#endif
                     sv[i][0] = __ldg(pa); sv[i][1] = __ldg(pa + 1);
                     sv[i][2] = __ldg(pa + pitch); sv[i][3] = __ldg(pa + pitch + 1);
                 }
