@@ -93,6 +93,12 @@ class ClockSampler:
     def mark(self):
         """Start of the timed region: drop what was sampled before it."""
         self.rows = []
+        self.n_region = None
+
+    def mark_end(self):
+        """End of the timed region; sampling goes on (the end-to-end legs run the same kernels) so that a
+        short --steps run still gets a reading."""
+        self.n_region = len(self.rows)
 
     def _read(self):
         for line in self.proc.stdout:
@@ -108,7 +114,14 @@ class ClockSampler:
             self.proc.kill()
         sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
+        n_region = getattr(self, "n_region", None)
+        window = "timed region"
+        rows = self.rows
+        if n_region is not None and n_region >= 3:
+            rows = self.rows[:n_region]
+        elif n_region is not None:
+            window = "timed region (%d samples) + the end-to-end legs after it" % n_region
+        for r in rows:
             f = [x.strip() for x in r.split(",")]
             if len(f) < 6:
                 continue
@@ -122,7 +135,7 @@ class ClockSampler:
                     reasons.add(nm)
         sm.sort()
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+                "reasons": sorted(reasons), "samples": len(sm), "window": window}
 
 
 _emit = print
@@ -252,7 +265,7 @@ def run_ours(args):
         step()
     e1.record()
     barrier()
-    clocks = sampler.stop()
+    sampler.mark_end()
     ms_total = e0.elapsed_time(e1)
     # per-launch durations of every kernel launched inside the timed region (events on the
     # launching stream, recorded by the library around each launch)
@@ -327,6 +340,7 @@ def run_ours(args):
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_u8_val = world * n8 * u8_steps / float(t.item())
+    clocks = sampler.stop()
 
     # ---- the reference's own window (3x3, r = 1; bit-exact path), device-resident like `value` ---
     r1 = None
