@@ -58,6 +58,9 @@ namespace {
 #define PH_IDLE16 80             // head start (in 1/16 chunks of 32 P4 tasks) of a V warp without a P1 row ...
 #define PH_O16 18                // ... and of an O warp, over a V warp with a P1 row
 #endif
+#ifndef PH_SUMDIFF
+#define PH_SUMDIFF 0      // 1: P1 stores A' + B' and B' - A', 9 instead of 19 adds per gradient triple; measured +0.6 %, not worth leaving filter2D's order
+#endif
 constexpr int PH_NT = 512;       // threads per CTA (16 warps; a warp = one row of 32 quads)
 constexpr int PH_NW = PH_NT / 32;
 constexpr int PH_PC = 128;       // product columns per strip = 32 lanes x 4 columns
@@ -259,8 +262,9 @@ __device__ __forceinline__ void phase_remap(const LevelArgs& a, const PGeo& g, c
             }
             // park the upsampled flow of output pixels for the epilogue (tmpu += upu, :634-637)
             if (vy == yy && vy >= g.y0 && vy < g.y1) {
-                double* pu = U + (size_t)vy * a.uv_pitch + x0;
-                double* pv = V + (size_t)vy * a.uv_pitch + x0;
+                const int off = vy * (int)a.uv_pitch + x0;
+                double* pu = U + off;
+                double* pv = V + off;
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
                     const int X = lane + 32 * i;
@@ -332,8 +336,14 @@ __device__ __forceinline__ void phase_remap(const LevelArgs& a, const PGeo& g, c
         for (int i = 0; i < 4; ++i) {
             const bool in = (inm >> i) & 1u;
             const int q = ppos(lane + 32 * i);
-            dst[q] = in ? va[i] : 0.0;
-            dst[AB_PITCH + q] = in ? vb[i] : 0.0;
+            if constexpr (R == 1 || !PH_SUMDIFF) {
+                dst[q] = in ? va[i] : 0.0;
+                dst[AB_PITCH + q] = in ? vb[i] : 0.0;
+            } else {
+                // R >= 2 (tolerance path): the gradients only need A' + B' and B' - A' (see P2)
+                dst[q] = in ? dadd(va[i], vb[i]) : 0.0;
+                dst[AB_PITCH + q] = in ? dsub(vb[i], va[i]) : 0.0;
+            }
         }
     }
 }
@@ -380,6 +390,20 @@ __device__ __forceinline__ void phase_products(const PGeo& g, int vy0, int sb, c
             pLA = pA[1]; pLB = pB[1]; cLA = cA[1]; cLB = cB[1];
         }
         double fx[4], fy[4], ft[4];
+#if PH_SUMDIFF
+        // the rows hold C = A' + B' and D = B' - A':  fx = dC/dx summed over the two rows, fy = dC/dy summed
+        // over the two columns, ft = D summed over the 2x2 cell (:44-84 up to the association of the adds)
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const double c00 = q ? pA[q - 1] : pLA, c01 = pA[q];
+            const double c10 = q ? cA[q - 1] : cLA, c11 = cA[q];
+            const double d00 = q ? pB[q - 1] : pLB, d01 = pB[q];
+            const double d10 = q ? cB[q - 1] : cLB, d11 = cB[q];
+            fx[q] = dadd(dsub(c01, c00), dsub(c11, c10));
+            fy[q] = dsub(dadd(c10, c11), dadd(c00, c01));
+            ft[q] = dadd(dadd(d00, d01), dadd(d10, d11));
+        }
+#else
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
             const double a00 = q ? pA[q - 1] : pLA, a01 = pA[q];
@@ -397,6 +421,7 @@ __device__ __forceinline__ void phase_products(const PGeo& g, int vy0, int sb, c
             fy[q] = dadd(fya, fyb);
             ft[q] = dadd(fta, ftb);
         }
+#endif
         if (g.edge) {                                        // columns outside the image contribute nothing
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
@@ -461,18 +486,19 @@ __device__ __forceinline__ void phase_vertical(double* col, double* vs)
 struct StatAcc { unsigned long long x, y, c; };
 
 // Solve + epilogue of output pixels (y, xb), (y, xb + 1) from their five window sums.
-template <int R>
+template <int R, bool VEC>
 __device__ __forceinline__ void solve_pair(const LevelArgs& a, const PGeo& g, double* __restrict__ U,
                                            double* __restrict__ V, unsigned char* __restrict__ M, int y, int xb,
                                            double2 sxx, double2 syy, double2 sxy, double2 sxt, double2 syt,
                                            double det_eps, double mag2, StatAcc& st)
 {
     const int W = g.W, H = g.H;
-    double* pu = U + (size_t)y * a.uv_pitch + xb;
-    double* pv = V + (size_t)y * a.uv_pitch + xb;
+    const int off = y * (int)a.uv_pitch + xb;            // < 2^31 (checked by the launcher)
+    double* pu = U + off;
+    double* pv = V + off;
     double upu[2] = {0.0, 0.0}, upv[2] = {0.0, 0.0};
     if (g.has_coarse) {                                  // parked by P1 (same CTA, barriers between)
-        if (g.vec_uv) {
+        if constexpr (VEC) {
             const double2 u0 = *reinterpret_cast<const double2*>(pu), v0 = *reinterpret_cast<const double2*>(pv);
             upu[0] = u0.x; upu[1] = u0.y; upv[0] = v0.x; upv[1] = v0.y;
         } else {
@@ -513,7 +539,7 @@ __device__ __forceinline__ void solve_pair(const LevelArgs& a, const PGeo& g, do
         fv[q] = ok ? lv[q] : 0.0;
         if (g.has_coarse) { fu[q] = dadd(fu[q], upu[q]); fv[q] = dadd(fv[q], upv[q]); }
     }
-    if (g.vec_uv) {
+    if constexpr (VEC) {
         *reinterpret_cast<double2*>(pu) = make_double2(fu[0], fu[1]);
         *reinterpret_cast<double2*>(pv) = make_double2(fv[0], fv[1]);
     } else {
@@ -537,7 +563,7 @@ __device__ __forceinline__ void solve_pair(const LevelArgs& a, const PGeo& g, do
     }
 }
 
-template <int R>
+template <int R, bool VEC>
 __device__ __forceinline__ void phase_solve(const LevelArgs& a, const PGeo& g, double* __restrict__ U,
                                             double* __restrict__ V, unsigned char* __restrict__ M, int m0,
                                             int i_lo, int i_hi, const double* s_prod, StatAcc& st, int t_begin,
@@ -547,9 +573,9 @@ __device__ __forceinline__ void phase_solve(const LevelArgs& a, const PGeo& g, d
     constexpr int NPAIR = C::OUT_COLS / 2;                   // task = (row, pair of columns)
     const int W = g.W;
     const double det_eps = a.det_eps, mag2 = a.mag2_thresh;
-    for (int t = t_begin; t < t_end; t += nthr) {
-        const int ir = t / NPAIR;
-        const int pr = t - ir * NPAIR;
+    int ir = t_begin / NPAIR, pr = t_begin - ir * NPAIR;
+    for (int t = t_begin; t < t_end; t += nthr, pr += nthr) {
+        if (pr >= NPAIR) { pr -= NPAIR; ++ir; }              // nthr = 32 <= NPAIR
         const int i = i_lo + ir;
         const int xb = g.xo0 + 2 * pr;                       // even; W even: both columns exist or none
         if (xb >= W) continue;
@@ -557,7 +583,7 @@ __device__ __forceinline__ void phase_solve(const LevelArgs& a, const PGeo& g, d
         const int y = g.y0 + m0 + i;
         const double2 sxx = lds2(sp), syy = lds2(sp + C::PPITCH), sxy = lds2(sp + 2 * C::PPITCH);
         const double2 sxt = lds2(sp + 3 * C::PPITCH), syt = lds2(sp + 4 * C::PPITCH);
-        solve_pair<R>(a, g, U, V, M, y, xb, sxx, syy, sxy, sxt, syt, det_eps, mag2, st);
+        solve_pair<R, VEC>(a, g, U, V, M, y, xb, sxx, syy, sxy, sxt, syt, det_eps, mag2, st);
     }
 }
 
@@ -639,6 +665,7 @@ __device__ __forceinline__ void phase_products1(const PGeo& g, int vy0, int sb, 
 // P4 for R = 1: the calling warp owns output row y (window rows in ring slots r0, r1, r2), lane
 // L (1 .. 30) the four output columns c0 + 4 L ..; 3x3 sums in get_Sum9's order (:122-157:
 // row-major, starting from 0.0), then the solve of both column pairs.
+template <bool VEC>
 __device__ __forceinline__ void phase_solve1(const LevelArgs& a, const PGeo& g, double* __restrict__ U,
                                              double* __restrict__ V, unsigned char* __restrict__ M, int y,
                                              int r0, int r1, int r2, const double* s_prod, StatAcc& st)
@@ -679,7 +706,7 @@ __device__ __forceinline__ void phase_solve1(const LevelArgs& a, const PGeo& g, 
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
         if (xb + 2 * h >= g.W) break;
-        solve_pair<1>(a, g, U, V, M, y, xb + 2 * h, make_double2(S[0][2 * h], S[0][2 * h + 1]),
+        solve_pair<1, VEC>(a, g, U, V, M, y, xb + 2 * h, make_double2(S[0][2 * h], S[0][2 * h + 1]),
                       make_double2(S[1][2 * h], S[1][2 * h + 1]), make_double2(S[2][2 * h], S[2][2 * h + 1]),
                       make_double2(S[3][2 * h], S[3][2 * h + 1]), make_double2(S[4][2 * h], S[4][2 * h + 1]), det_eps,
                       mag2, st);
@@ -687,7 +714,7 @@ __device__ __forceinline__ void phase_solve1(const LevelArgs& a, const PGeo& g, 
 }
 
 // ------------------------------------------------------------------------------ kernel
-template <int R>
+template <int R, bool VEC>
 __global__ void __launch_bounds__(PH_NT, 1) lk_level_phase_kernel(LevelArgs a, int th)
 {
     using C = PhaseCfg<R>;
@@ -833,7 +860,7 @@ __global__ void __launch_bounds__(PH_NT, 1) lk_level_phase_kernel(LevelArgs a, i
             c0 = min(c0, nch);
             c1 = min(c1, nch);
             PH_MARK(4);
-            phase_solve<R>(a, g, U, V, M, m0, i_lo, i_hi, s_prod, st, 32 * c0 + (threadIdx.x & 31), min(32 * c1, n4), 32);
+            phase_solve<R, VEC>(a, g, U, V, M, m0, i_lo, i_hi, s_prod, st, 32 * c0 + (threadIdx.x & 31), min(32 * c1, n4), 32);
         }
         PH_MARK(5);
         __syncthreads();
@@ -852,7 +879,7 @@ __global__ void __launch_bounds__(PH_NT, 1) lk_level_phase_kernel(LevelArgs a, i
             st.y += __shfl_xor_sync(0xffffffffu, st.y, o);
             st.c += __shfl_xor_sync(0xffffffffu, st.c, o);
         }
-        if ((threadIdx.x & 31) == 0 && st.c != 0) {    // integer-valued sums: exact in any order
+        if ((threadIdx.x & 31) == 0 && st.c != 0) {   // integer-valued sums: exact in any order
             atomicAdd(&a.stats[pair].sum_x, (double)st.x);
             atomicAdd(&a.stats[pair].sum_y, (double)st.y);
             atomicAdd(&a.stats[pair].count, (double)st.c);
@@ -867,6 +894,7 @@ __global__ void __launch_bounds__(PH_NT, 1) lk_level_phase_kernel(LevelArgs a, i
 //          solve first, so that the latency-bound gathers of one half overlap the FP64 work
 //          of the other.
 // Output row n - 2 (relative to y0) is produced when product row n = s WIN + i has arrived.
+template <bool VEC>
 __global__ void __launch_bounds__(PhaseCfg<1>::NT, PhaseCfg<1>::CTAS) lk_level_phase1_kernel(LevelArgs a, int th)
 {
     constexpr int R = 1;
@@ -950,11 +978,11 @@ __global__ void __launch_bounds__(PhaseCfg<1>::NT, PhaseCfg<1>::CTAS) lk_level_p
 #define PH1_SOLVE_FIRST (warp < C::NT / 64)      // two solve-first and two remap-first warps per SM sub-partition
 #endif
         if (PH1_SOLVE_FIRST) {
-            if (solve) phase_solve1(a, g, U, V, M, g.y0 + n - 2, r0, r1, r2, s_prod, st);
+            if (solve) phase_solve1<VEC>(a, g, U, V, M, g.y0 + n - 2, r0, r1, r2, s_prod, st);
             phase_remap<R>(a, g, A, B, U, V, nxt.vy0, r_mine, C::WIN + 1, nxt.sb, s_hr, s_ab);
         } else {
             phase_remap<R>(a, g, A, B, U, V, nxt.vy0, r_mine, C::WIN + 1, nxt.sb, s_hr, s_ab);
-            if (solve) phase_solve1(a, g, U, V, M, g.y0 + n - 2, r0, r1, r2, s_prod, st);
+            if (solve) phase_solve1<VEC>(a, g, U, V, M, g.y0 + n - 2, r0, r1, r2, s_prod, st);
         }
         __syncthreads();
         cur = nxt;
@@ -975,17 +1003,18 @@ __global__ void __launch_bounds__(PhaseCfg<1>::NT, PhaseCfg<1>::CTAS) lk_level_p
     }
 }
 
-template <int R>
-cudaError_t launch_phase(const LevelArgs& a, int n_pairs, cudaStream_t s, unsigned long long* launches)
+template <int R, bool VEC>
+cudaError_t launch_phase_v(const LevelArgs& a, int n_pairs, cudaStream_t s, unsigned long long* launches)
 {
     using C = PhaseCfg<R>;
     static bool attr_done = false;
     if (!attr_done) {
         cudaError_t e;
         if constexpr (R == 1)
-            e = cudaFuncSetAttribute(lk_level_phase1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM_BYTES);
+            e = cudaFuncSetAttribute(lk_level_phase1_kernel<VEC>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)C::SMEM_BYTES);
         else
-            e = cudaFuncSetAttribute(lk_level_phase_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+            e = cudaFuncSetAttribute(lk_level_phase_kernel<R, VEC>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      (int)C::SMEM_BYTES);
         if (e != cudaSuccess) return e;
         attr_done = true;
@@ -1011,10 +1040,20 @@ cudaError_t launch_phase(const LevelArgs& a, int n_pairs, cudaStream_t s, unsign
     }
     const int chunks = (a.h + th - 1) / th;
     dim3 grid(strips, chunks, n_pairs);
-    if constexpr (R == 1) lk_level_phase1_kernel<<<grid, nt, C::SMEM_BYTES, s>>>(a, th);
-    else lk_level_phase_kernel<R><<<grid, PH_NT, C::SMEM_BYTES, s>>>(a, th);
+    if constexpr (R == 1) lk_level_phase1_kernel<VEC><<<grid, nt, C::SMEM_BYTES, s>>>(a, th);
+    else lk_level_phase_kernel<R, VEC><<<grid, nt, C::SMEM_BYTES, s>>>(a, th);
     if (launches) *launches += 1;
     return cudaGetLastError();
+}
+
+// VEC: every flow row of every pair is 16-byte aligned (true for the library's own planes and for dense
+// caller buffers), so the epilogue uses 16-byte accesses without a second, predicated code path.
+template <int R>
+cudaError_t launch_phase(const LevelArgs& a, int n_pairs, cudaStream_t s, unsigned long long* launches)
+{
+    const bool vec = ((reinterpret_cast<uintptr_t>(a.u) | reinterpret_cast<uintptr_t>(a.v) | (a.uv_pitch * 8) |
+                       (n_pairs > 1 ? a.uv_pair_stride * 8 : 0)) & 15) == 0;
+    return vec ? launch_phase_v<R, true>(a, n_pairs, s, launches) : launch_phase_v<R, false>(a, n_pairs, s, launches);
 }
 
 }  // namespace
@@ -1029,6 +1068,7 @@ cudaError_t launch_lk_level_phase(const LevelArgs& a, int n_pairs, cudaStream_t 
     if (a.w < 4 || a.h < 2 || (a.w & 1)) return cudaSuccess;
     if (a.cu && (a.wc < 2 || a.w != 2 * a.wc || a.h != 2 * a.hc)) return cudaSuccess;
     if ((unsigned long long)a.img_pitch * (unsigned long long)a.h >= (1ull << 31)) return cudaSuccess;
+    if ((unsigned long long)a.uv_pitch * (unsigned long long)a.h >= (1ull << 31)) return cudaSuccess;
     *handled = true;
     switch (a.radius) {
         case 1: return launch_phase<1>(a, n_pairs, s, launches);

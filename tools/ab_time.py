@@ -11,13 +11,14 @@ synth = importlib.import_module("optical_flow_b200.synth")
 h, w, L, r, n = 1080, 1920, 3, int(os.environ.get("AB_R", "7")), 16
 fr = torch.from_numpy(synth.synth_frames(n + 1, h, w, seed=1234)).cuda()
 U = torch.empty((n, h, w), dtype=torch.float64, device="cuda"); V = torch.empty_like(U)
+S = torch.zeros((n, 4), dtype=torch.float64, device="cuda") if os.environ.get("AB_STATS", "1") == "1" else None
 with ofb.Context(0, win_radius=r) as ctx:
-    for _ in range(3): ctx.flow_batch_dev(fr, L, U, V)
+    for _ in range(3): ctx.flow_batch_dev(fr, L, U, V, S)
     torch.cuda.synchronize()
     ctx.set_timing(True)
     e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
     e0.record()
-    for _ in range(10): ctx.flow_batch_dev(fr, L, U, V)
+    for _ in range(10): ctx.flow_batch_dev(fr, L, U, V, S)
     e1.record(); torch.cuda.synchronize()
     t = ctx.get_timing()
     l0 = [ms for k, l, ms in t if k == 1 and l == 0]; l1 = [ms for k, l, ms in t if k == 1 and l == 1]; l2 = [ms for k, l, ms in t if k == 1 and l == 2]
