@@ -231,6 +231,29 @@ def test_error_codes(ofb):
 
 
 # ------------------------------------------------------------------ device / batch / stream
+@pytest.mark.parametrize("r", [1, 7])
+def test_misaligned_device_views(ofb, c_oracle, torch_cuda, r):
+    """Device-pointer call on ROI views whose rows are only 8-byte aligned (odd column offset, odd
+    pitch): the level kernels take their non-vectorised epilogue (VEC = false) and still match."""
+    torch = torch_cuda
+    fr = ofb_synth().synth_frames(2, 90, 164, seed=11)
+    big = torch.zeros((2, 92, 167), dtype=torch.float64, device="cuda")
+    big[:, 1:91, 3:167] = torch.from_numpy(fr).cuda()
+    a, b = big[0, 1:91, 3:167], big[1, 1:91, 3:167]
+    out = torch.full((2, 92, 167), 7.0, dtype=torch.float64, device="cuda")
+    u, v = out[0, 1:91, 1:165], out[1, 1:91, 1:165]
+    assert (u.stride(0) * 8) % 16 == 8                      # every other row starts 8 bytes off a 16-byte boundary
+    with ofb.Context(0, win_radius=r) as ctx:
+        ctx.coarseToFineEstimation_dev(a, b, 2, u, v)
+        torch.cuda.synchronize()
+    uo, vo = c_oracle.coarse_to_fine(fr[0], fr[1], 2, r)
+    err = max(np.abs(u.cpu().numpy() - uo).max(), np.abs(v.cpu().numpy() - vo).max())
+    assert err <= (0.0 if r == 1 else FLOW_TOL)
+    o = out.cpu().numpy()                                   # nothing outside the views was touched
+    assert (o[:, 0, :] == 7.0).all() and (o[:, 91, :] == 7.0).all() and (o[:, :, 0] == 7.0).all()
+    assert (o[:, :, 165:] == 7.0).all()
+
+
 def test_device_and_batch_entry_points(ofb, c_oracle, torch_cuda):
     torch = torch_cuda
     fr = ofb_synth().synth_frames(5, 96, 160, seed=3)
