@@ -1058,8 +1058,8 @@ cudaError_t launch_phase(const LevelArgs& a, int n_pairs, cudaStream_t s, unsign
 
 }  // namespace
 
-// Handles R = 2..7 on even-width levels with a flow output; everything else (R = 1 bit-exact
-// order, tiny levels, statistics-only calls) goes to the other kernels.
+// Handles R = 1..7 on even-width levels (statistics-only calls come with scratch flow planes from the
+// caller, of_api.cu); tiny / odd-sized levels and larger radii go to the other kernels.
 cudaError_t launch_lk_level_phase(const LevelArgs& a, int n_pairs, cudaStream_t s,
                                   unsigned long long* launches, bool* handled)
 {

@@ -127,7 +127,9 @@ struct Plan {
     size_t total = 0;
 };
 
-Plan make_plan(int w, int h, int L, int n_pairs, bool shared)
+// l0_flow: statistics-only calls (u = v = NULL) get scratch level-0 flow planes, so that they run on the
+// same throughput kernels as calls that return the flow (those park the upsampled flow in u, v).
+Plan make_plan(int w, int h, int L, int n_pairs, bool shared, bool l0_flow)
 {
     Plan p;
     p.L = L;
@@ -148,6 +150,8 @@ Plan make_plan(int w, int h, int L, int n_pairs, bool shared)
         if (l >= 1) {
             p.pyr_off[l] = off;
             off += g.img_stride * p.n_frames * sizeof(double);
+        }
+        if (l >= 1 || l0_flow) {
             p.flow_u_off[l] = off;
             off += g.img_stride * n_pairs * sizeof(double);
             p.flow_v_off[l] = off;
@@ -266,7 +270,7 @@ of_status run_batch(of_ctx* ctx, int n_pairs, const double* img1, const double* 
     OF_CUDA(ctx, cudaSetDevice(ctx->device));
 
     const bool shared = n_pairs > 1 && (const char*)img2 == (const char*)img1 + img_pair_stride;
-    Plan p = make_plan(w, h, L, n_pairs, shared);
+    Plan p = make_plan(w, h, L, n_pairs, shared, u == nullptr);
     st = arena_reserve(ctx, ctx->scratch, p.total);
     if (st) return st;
     char* base = ctx->scratch.base;
@@ -352,10 +356,17 @@ of_status run_batch(of_ctx* ctx, int n_pairs, const double* img1, const double* 
             a.hc = gc.h;
         }
         if (l == 0) {
-            a.u = u;
-            a.v = v;
-            a.uv_pitch = uv_step / sizeof(double);
-            a.uv_pair_stride = uv_pair_stride / sizeof(double);
+            if (u) {
+                a.u = u;
+                a.v = v;
+                a.uv_pitch = uv_step / sizeof(double);
+                a.uv_pair_stride = uv_pair_stride / sizeof(double);
+            } else {                                   // statistics / mask only: scratch flow planes
+                a.u = (double*)(base + p.flow_u_off[0]);
+                a.v = (double*)(base + p.flow_v_off[0]);
+                a.uv_pitch = g.pitch;
+                a.uv_pair_stride = g.img_stride;
+            }
             a.mask = mask;
             a.mask_pitch = mask_step;
             a.mask_pair_stride = mask_pair_stride;
@@ -749,7 +760,7 @@ of_status of_ctf_f64(of_ctx* ctx, double* img1, double* img2, int width, int hei
         OF_CUDA(ctx, cudaMemcpy2DAsync(mask, mask_step_bytes, dm, pitch, (size_t)width, height, cudaMemcpyDeviceToHost, s));
     if (ctx->params.write_back_warped && n_levels > 1) {
         // Quirk Q1: the reference leaves the warped level-0 frames in the caller's buffers.
-        Plan p = make_plan(width, height, n_levels, 1, false);
+        Plan p = make_plan(width, height, n_levels, 1, false, false);
         ofb::WarpArgs a{};
         a.cu = (const double*)(ctx->scratch.base + p.flow_u_off[1]);
         a.cv = (const double*)(ctx->scratch.base + p.flow_v_off[1]);
