@@ -82,6 +82,27 @@ def run(name, frames, L, r, pairs_mode, cpu_pairs, reps):
             "max_abs_diff_vs_port_last_sampled_pair": float(err)}
 
 
+def latency(name, frames, L, r, reps=200):
+    """One pair per call (what the reference's live loop does, ParallelVideoPyr.cpp:831-832), device-resident."""
+    h, w = frames.shape[1:]
+    d = torch.from_numpy(np.ascontiguousarray(frames[:2])).cuda()
+    u = torch.empty((h, w), dtype=torch.float64, device="cuda")
+    v = torch.empty_like(u)
+    with ofb.Context(0, win_radius=r) as ctx:
+        for _ in range(5):
+            ctx.coarseToFineEstimation_dev(d[0], d[1], L, u, v)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            ctx.coarseToFineEstimation_dev(d[0], d[1], L, u, v)
+        e1.record()
+        torch.cuda.synchronize()
+    us = e0.elapsed_time(e1) / reps * 1e3
+    return {"config": name, "width": w, "height": h, "levels": L, "win_radius": r, "pairs_per_call": 1,
+            "us_per_call_back_to_back": us, "gpu_pairs_per_s": 1e6 / us}
+
+
 def main():
     out = []
     hand = np.stack([gray_png("hand1_gray.png"), gray_png("hand2_gray.png")])
@@ -100,6 +121,10 @@ def main():
     f = synth.synth_frames(9, 2160, 3840, seed=1234)
     out.append(run("synthetic 4K L=4, 15x15 (configs[4], one GPU's share)", f, 4, 7, "stream", 2, 10))
     out.append(run("synthetic 4K L=4, 3x3 (configs[4])", f, 4, 1, "stream", 2, 10))
+    f = synth.synth_frames(2, 1080, 1080, seed=1234)
+    out.append(latency("one pair per call, 1080x1080 L=4 3x3 (the live loop's call)", f, 4, 1))
+    f = synth.synth_frames(2, 1080, 1920, seed=1234)
+    out.append(latency("one pair per call, 1080p L=3 15x15", f, 3, 7))
     json.dump({"hbm_peak_gbs": PEAK, "gpu": torch.cuda.get_device_name(0), "results": out}, sys.stdout, indent=1)
     print()
 
