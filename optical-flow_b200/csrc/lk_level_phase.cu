@@ -58,9 +58,6 @@ namespace {
 #define PH_IDLE16 80             // head start (in 1/16 chunks of 32 P4 tasks) of a V warp without a P1 row ...
 #define PH_O16 18                // ... and of an O warp, over a V warp with a P1 row
 #endif
-#ifndef PH_SUMDIFF
-#define PH_SUMDIFF 0      // 1: P1 stores A' + B' and B' - A', 9 instead of 19 adds per gradient triple; measured +0.6 %, not worth leaving filter2D's order
-#endif
 constexpr int PH_NT = 512;       // threads per CTA (16 warps; a warp = one row of 32 quads)
 constexpr int PH_NW = PH_NT / 32;
 constexpr int PH_PC = 128;       // product columns per strip = 32 lanes x 4 columns
@@ -336,14 +333,8 @@ __device__ __forceinline__ void phase_remap(const LevelArgs& a, const PGeo& g, c
         for (int i = 0; i < 4; ++i) {
             const bool in = (inm >> i) & 1u;
             const int q = ppos(lane + 32 * i);
-            if constexpr (R == 1 || !PH_SUMDIFF) {
-                dst[q] = in ? va[i] : 0.0;
-                dst[AB_PITCH + q] = in ? vb[i] : 0.0;
-            } else {
-                // R >= 2 (tolerance path): the gradients only need A' + B' and B' - A' (see P2)
-                dst[q] = in ? dadd(va[i], vb[i]) : 0.0;
-                dst[AB_PITCH + q] = in ? dsub(vb[i], va[i]) : 0.0;
-            }
+            dst[q] = in ? va[i] : 0.0;
+            dst[AB_PITCH + q] = in ? vb[i] : 0.0;
         }
     }
 }
@@ -390,20 +381,6 @@ __device__ __forceinline__ void phase_products(const PGeo& g, int vy0, int sb, c
             pLA = pA[1]; pLB = pB[1]; cLA = cA[1]; cLB = cB[1];
         }
         double fx[4], fy[4], ft[4];
-#if PH_SUMDIFF
-        // the rows hold C = A' + B' and D = B' - A':  fx = dC/dx summed over the two rows, fy = dC/dy summed
-        // over the two columns, ft = D summed over the 2x2 cell (:44-84 up to the association of the adds)
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-            const double c00 = q ? pA[q - 1] : pLA, c01 = pA[q];
-            const double c10 = q ? cA[q - 1] : cLA, c11 = cA[q];
-            const double d00 = q ? pB[q - 1] : pLB, d01 = pB[q];
-            const double d10 = q ? cB[q - 1] : cLB, d11 = cB[q];
-            fx[q] = dadd(dsub(c01, c00), dsub(c11, c10));
-            fy[q] = dsub(dadd(c10, c11), dadd(c00, c01));
-            ft[q] = dadd(dadd(d00, d01), dadd(d10, d11));
-        }
-#else
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
             const double a00 = q ? pA[q - 1] : pLA, a01 = pA[q];
@@ -421,7 +398,6 @@ __device__ __forceinline__ void phase_products(const PGeo& g, int vy0, int sb, c
             fy[q] = dadd(fya, fyb);
             ft[q] = dadd(fta, ftb);
         }
-#endif
         if (g.edge) {                                        // columns outside the image contribute nothing
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
