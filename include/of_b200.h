@@ -16,7 +16,11 @@
  *
  * All functions are extern "C", POD-only, and never throw.  A context is bound to one
  * CUDA device and is not thread-safe; distinct contexts may be used concurrently from
- * distinct threads/processes (the multi-GPU model: one process or thread per GPU).
+ * distinct threads/processes (the multi-GPU model: one process or thread per GPU; the
+ * of_mgpu_* calls below do exactly that inside one process).
+ * Streams: all calls on one context share its device scratch (pyramids, per-level flows).
+ * Calls are ordered against each other whatever stream they are given: a call on a stream
+ * other than the previous call's waits (on the device) for that call's kernels first.
  * There is NO CPU fallback: if no CUDA device is usable, of_ctx_create fails with
  * OF_E_CUDA.
  */
@@ -57,6 +61,8 @@ typedef struct of_params {
     int write_back_warped; /* 1: host-pointer of_ctf_f64 overwrites img1/img2 with their      */
                            /* warped level-0 versions like the reference does (quirk Q1,      */
                            /* warped.copyTo(pyr[i-1]) :696,701).  Default 0: inputs const.    */
+                           /* The _dev, batch and stream calls take const inputs and return   */
+                           /* OF_E_BADARG when the flag is 1 and n_levels > 1.                */
     double mag_thresh;     /* gesture statistics: flow magnitude threshold, reference 20 (:859)*/
     int count_thresh;      /* gesture present iff count > count_thresh, reference 500 (:886)  */
 } of_params;

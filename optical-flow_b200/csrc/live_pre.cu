@@ -161,11 +161,10 @@ template <int N>
 cudaError_t launch_live_n(const LiveDiffArgs& a, cudaStream_t s, unsigned long long* launches)
 {
     using C = LiveCfg<N>;
-    static bool attr_done = false;
-    if (!attr_done && C::SMEM > 48 * 1024) {
-        cudaError_t e = cudaFuncSetAttribute(live_diff_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM);
+    static SmemOptIn opt_in;
+    if (C::SMEM > 48 * 1024) {
+        cudaError_t e = opt_in.ensure((const void*)live_diff_kernel<N>, C::SMEM);
         if (e != cudaSuccess) return e;
-        attr_done = true;
     }
     dim3 grid((a.w + LT - 1) / LT, (a.h + LT - 1) / LT, 1);
     live_diff_kernel<N><<<grid, 256, C::SMEM, s>>>(a.cur, a.prev, a.gray_step, a.w, a.h, a.beta, a.thresh, a.out, a.out_pitch);

@@ -983,25 +983,20 @@ template <int R, bool VEC>
 cudaError_t launch_phase_v(const LevelArgs& a, int n_pairs, cudaStream_t s, unsigned long long* launches)
 {
     using C = PhaseCfg<R>;
-    static bool attr_done = false;
-    if (!attr_done) {
+    static SmemOptIn opt_in;
+    {
         cudaError_t e;
-        if constexpr (R == 1)
-            e = cudaFuncSetAttribute(lk_level_phase1_kernel<VEC>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     (int)C::SMEM_BYTES);
-        else
-            e = cudaFuncSetAttribute(lk_level_phase_kernel<R, VEC>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     (int)C::SMEM_BYTES);
+        if constexpr (R == 1) e = opt_in.ensure((const void*)lk_level_phase1_kernel<VEC>, C::SMEM_BYTES);
+        else e = opt_in.ensure((const void*)lk_level_phase_kernel<R, VEC>, C::SMEM_BYTES);
         if (e != cudaSuccess) return e;
-        attr_done = true;
     }
     const int strips = (a.w + C::OUT_COLS - 1) / C::OUT_COLS;
     // Chunk height: a multiple of the vertical block length, so that block boundaries sit at
     // the same absolute rows whatever the chunking (bit-identical results for any batch size).
     // Pick the height that minimises (waves of resident CTAs) x (steps a CTA runs).
-    long resident = 148;
+    long resident = current_sm_count();
     int nt = PH_NT;
-    if constexpr (R == 1) { resident = 148 * C::CTAS; nt = C::NT; }
+    if constexpr (R == 1) { resident *= C::CTAS; nt = C::NT; }
     const int max_m = (a.h + C::WIN - 1) / C::WIN;
     long best_cost = -1;
     int th = C::WIN * max_m;

@@ -247,12 +247,9 @@ __global__ void __launch_bounds__(TL_NT) lk_level_tile_kernel(LevelArgs a, int t
 cudaError_t launch_lk_level_tile(const LevelArgs& a, int n_pairs, cudaStream_t s,
                                  unsigned long long* launches)
 {
-    static int max_smem = -1;
-    if (max_smem < 0) {
-        int dev = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
-    }
+    int max_smem = 0, dev = 0;                      // per device: queried on every launch (this is the rare path)
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
     int th = 32;
     while (th > 1 && TileGeom(a.radius, th).smem_doubles() * sizeof(double) + 1024 > (size_t)max_smem) th >>= 1;
     const size_t smem = TileGeom(a.radius, th).smem_doubles() * sizeof(double);

@@ -23,8 +23,6 @@ cudaError_t launch_lk_level_tile(const LevelArgs& a, int n_pairs, cudaStream_t s
                                  unsigned long long* launches);
 cudaError_t launch_lk_level_phase(const LevelArgs& a, int n_pairs, cudaStream_t s,
                                   unsigned long long* launches, bool* handled);
-cudaError_t launch_lk_level_strip(const LevelArgs& a, int n_pairs, cudaStream_t s,
-                                  unsigned long long* launches, bool* handled);
 }  // namespace ofb
 
 namespace {
@@ -55,7 +53,7 @@ struct of_ctx {
     size_t h_stats_cap = 0;               // (a copy into pageable memory would block the host thread)
     std::string err;
     unsigned long long launches = 0;
-    int force_variant = 0;             // 0 auto, 1 tile, 3 strip, 4 phase (test hook via OF_B200_VARIANT)
+    int force_variant = 0;             // 0 auto, 1 tile, 4 phase (test hook via OF_B200_VARIANT)
     // optional per-launch device timing of the most recent batch call (bench roofline evidence)
     bool timing = false;
     std::vector<cudaEvent_t> tev;      // 2 events per timed launch
@@ -66,7 +64,12 @@ struct of_ctx {
     std::vector<LastLevel> last;
     int last_pairs = 0;
     bool last_shared = false;
+    // The scratch arena is shared by every call on this context: ev_scratch marks the end of the most
+    // recent batch on the stream it ran on (last_stream), so that a call on a different stream waits
+    // for it instead of overwriting pyramids / flows that are still being read.
     cudaStream_t last_stream = nullptr;
+    cudaEvent_t ev_scratch = nullptr;
+    bool scratch_busy = false;
 };
 
 namespace {
@@ -179,6 +182,17 @@ of_status check_common(of_ctx* ctx, const void* a, const void* b, int w, int h, 
     return OF_OK;
 }
 
+// One validation for of_ctx_create and of_ctx_set_params.
+const char* validate_params(const of_params& p)
+{
+    if (p.win_radius < 1 || p.win_radius > 15) return "win_radius must be in 1..15";
+    if (!(p.det_eps >= 0.0) || std::isinf(p.det_eps)) return "det_eps must be finite and >= 0";
+    if (p.write_back_warped != 0 && p.write_back_warped != 1) return "write_back_warped must be 0 or 1";
+    if (p.mag_thresh != p.mag_thresh) return "mag_thresh is NaN";
+    if (p.count_thresh < 0) return "count_thresh must be >= 0";
+    return nullptr;
+}
+
 // Smallest double s with !(sqrt(s) < t), so that  !(sqrt(s2) < t)  <=>  !(s2 < s)  for every
 // s2 >= 0 (sqrt is correctly rounded and monotonic).  Gesture statistics, :850-873.
 double mag2_threshold(double t)
@@ -238,11 +252,6 @@ cudaError_t launch_lk_level(of_ctx* ctx, const ofb::LevelArgs& a, int n_pairs, c
         cudaError_t e = ofb::launch_lk_level_phase(a, n_pairs, s, &ctx->launches, &handled);
         if (handled || e != cudaSuccess) return e;
     }
-    if (ctx->force_variant == 0 || ctx->force_variant == 3 || ctx->force_variant == 4) {
-        bool handled = false;
-        cudaError_t e = ofb::launch_lk_level_strip(a, n_pairs, s, &ctx->launches, &handled);
-        if (handled || e != cudaSuccess) return e;
-    }
     return ofb::launch_lk_level_tile(a, n_pairs, s, &ctx->launches);
 }
 
@@ -261,6 +270,10 @@ of_status run_batch(of_ctx* ctx, int n_pairs, const double* img1, const double* 
     if (u && (uv_step % sizeof(double) || uv_step < (size_t)w * sizeof(double)))
         return fail(ctx, OF_E_BADARG, "uv_step_bytes %zu invalid for width %d", uv_step, w);
     if (mask && mask_step < (size_t)w) return fail(ctx, OF_E_BADARG, "mask_step_bytes %zu < width", mask_step);
+    if (mask && n_pairs > 1 && mask_pair_stride < mask_step * (size_t)(h - 1) + (size_t)w)
+        return fail(ctx, OF_E_BADARG, "mask_pair_stride_bytes %zu is smaller than one mask plane", mask_pair_stride);
+    if (u && n_pairs > 1 && uv_pair_stride < uv_step * (size_t)(h - 1) + (size_t)w * sizeof(double))
+        return fail(ctx, OF_E_BADARG, "uv_pair_stride_bytes %zu is smaller than one flow plane", uv_pair_stride);
     if (n_pairs > 1 && img_pair_stride % sizeof(double))
         return fail(ctx, OF_E_BADARG, "img_pair_stride_bytes must be a multiple of 8");
     if (u && n_pairs > 1 && uv_pair_stride % sizeof(double))
@@ -268,6 +281,8 @@ of_status run_batch(of_ctx* ctx, int n_pairs, const double* img1, const double* 
     if (ctx->params.win_radius < 1 || ctx->params.win_radius > 15)
         return fail(ctx, OF_E_BADARG, "win_radius must be in 1..15");
     OF_CUDA(ctx, cudaSetDevice(ctx->device));
+    // scratch hand-over between streams (see of_ctx::ev_scratch)
+    if (ctx->scratch_busy && ctx->last_stream != s) OF_CUDA(ctx, cudaStreamWaitEvent(s, ctx->ev_scratch, 0));
 
     const bool shared = n_pairs > 1 && (const char*)img2 == (const char*)img1 + img_pair_stride;
     Plan p = make_plan(w, h, L, n_pairs, shared, u == nullptr);
@@ -382,6 +397,17 @@ of_status run_batch(of_ctx* ctx, int n_pairs, const double* img1, const double* 
     }
     if (stats)
         OF_CUDA(ctx, ofb::launch_stats_finalize(stats, n_pairs, (double)ctx->params.count_thresh, s, &ctx->launches));
+    OF_CUDA(ctx, cudaEventRecord(ctx->ev_scratch, s));
+    ctx->scratch_busy = true;
+    return OF_OK;
+}
+
+// The device-pointer, batch and stream entry points read their inputs through const pointers and cannot
+// leave the warped frames in them (quirk Q1); only the host-pointer of_ctf_f64 honours the flag.
+of_status reject_write_back(of_ctx* ctx, int n_levels, const char* who)
+{
+    if (ctx->params.write_back_warped && n_levels > 1)
+        return fail(ctx, OF_E_BADARG, "%s cannot honour write_back_warped = 1 (inputs are const); use of_ctf_f64", who);
     return OF_OK;
 }
 
@@ -434,16 +460,22 @@ of_status of_ctx_create(int device, const of_params* params, of_ctx** out)
     if (!ctx) return fail(nullptr, OF_E_NOMEM, "out of host memory");
     ctx->device = device;
     of_params_default(&ctx->params);
-    if (params) ctx->params = *params;
+    if (params) {
+        if (const char* why = validate_params(*params)) {
+            delete ctx;
+            return fail(nullptr, OF_E_BADARG, "%s", why);
+        }
+        ctx->params = *params;
+    }
     if (const char* fv = getenv("OF_B200_VARIANT")) {
         if (!strcmp(fv, "tile")) ctx->force_variant = 1;
-        else if (!strcmp(fv, "strip")) ctx->force_variant = 3;
         else if (!strcmp(fv, "phase")) ctx->force_variant = 4;
     }
     e = cudaSetDevice(device);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->down_stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ctx->ev_scratch, cudaEventDisableTiming);
     for (int i = 0; i < 2 && e == cudaSuccess; ++i) {
         e = cudaEventCreateWithFlags(&ctx->ev_up[i], cudaEventDisableTiming);
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ctx->ev_done[i], cudaEventDisableTiming);
@@ -467,6 +499,7 @@ void of_ctx_destroy(of_ctx* ctx)
     if (ctx->staging.base) cudaFree(ctx->staging.base);
     if (ctx->h_stats) cudaFreeHost(ctx->h_stats);
     for (cudaEvent_t e : ctx->tev) cudaEventDestroy(e);
+    if (ctx->ev_scratch) cudaEventDestroy(ctx->ev_scratch);
     for (int i = 0; i < 2; ++i) {
         if (ctx->ev_up[i]) cudaEventDestroy(ctx->ev_up[i]);
         if (ctx->ev_done[i]) cudaEventDestroy(ctx->ev_done[i]);
@@ -481,8 +514,7 @@ void of_ctx_destroy(of_ctx* ctx)
 of_status of_ctx_set_params(of_ctx* ctx, const of_params* params)
 {
     if (!ctx || !params) return OF_E_BADARG;
-    if (params->win_radius < 1 || params->win_radius > 15) return fail(ctx, OF_E_BADARG, "win_radius must be in 1..15");
-    if (!(params->det_eps >= 0.0)) return fail(ctx, OF_E_BADARG, "det_eps must be >= 0");
+    if (const char* why = validate_params(*params)) return fail(ctx, OF_E_BADARG, "%s", why);
     ctx->params = *params;
     return OF_OK;
 }
@@ -538,7 +570,7 @@ of_status of_ctx_get_level_f64(of_ctx* ctx, int what, int level, int pair, doubl
     else
         src = (const double*)(base + (what == OF_LEVEL_FLOW_U ? g.flow_u_off : g.flow_v_off)) + g.img_stride * pair;
     OF_CUDA(ctx, cudaSetDevice(ctx->device));
-    OF_CUDA(ctx, cudaStreamSynchronize(ctx->last_stream));
+    OF_CUDA(ctx, cudaEventSynchronize(ctx->ev_scratch));     // not the stream: the caller may have destroyed it
     OF_CUDA(ctx, cudaMemcpy2D(dst, dst_step_bytes, src, g.pitch * sizeof(double), (size_t)g.w * sizeof(double), g.h,
                               cudaMemcpyDefault));
     return OF_OK;
@@ -562,6 +594,7 @@ of_status of_ctf_f64_batch_dev(of_ctx* ctx, int n_pairs, const double* img1, con
                                size_t mask_step_bytes, of_gesture_stats* stats, void* stream)
 {
     if (!ctx) return OF_E_BADARG;
+    if (of_status st = reject_write_back(ctx, n_levels, "of_ctf_f64_batch_dev")) return st;
     return run_batch(ctx, n_pairs, img1, img2, img_pair_stride_bytes, width, height, step_bytes,
                      n_levels, u, v, uv_pair_stride_bytes, uv_step_bytes, mask,
                      mask_pair_stride_bytes, mask_step_bytes, stats, pick(ctx, stream));
@@ -574,6 +607,7 @@ of_status of_ctf_f64_dev(of_ctx* ctx, const double* img1, const double* img2, in
 {
     if (!ctx) return OF_E_BADARG;
     if (!u || !v) return fail(ctx, OF_E_BADARG, "null flow pointer");
+    if (of_status st = reject_write_back(ctx, n_levels, "of_ctf_f64_dev")) return st;
     return run_batch(ctx, 1, img1, img2, 0, width, height, step_bytes, n_levels, u, v, 0,
                      uv_step_bytes, mask, 0, mask_step_bytes, nullptr, pick(ctx, stream));
 }
@@ -805,6 +839,7 @@ static of_status stream_impl(of_ctx* ctx, const void* frames, size_t esz, double
     of_status st = esz == 8 ? check_common(ctx, (const double*)frames, (const double*)frames, width, height, step_bytes, n_levels)
                             : check_common(ctx, (const double*)frames, (const double*)frames, width, height, 8 * step_bytes, n_levels);
     if (st) return st;
+    if ((st = reject_write_back(ctx, n_levels, "the stream entry point"))) return st;
     if (n_frames < 2) return fail(ctx, OF_E_BADARG, "n_frames must be >= 2");
     if ((u == nullptr) != (v == nullptr)) return fail(ctx, OF_E_BADARG, "u and v must both be given or both be NULL");
     if (!u && !stats) return fail(ctx, OF_E_BADARG, "nothing to compute: u, v and stats are all NULL");
@@ -876,8 +911,10 @@ static of_status stream_impl(of_ctx* ctx, const void* frames, size_t esz, double
             // 8-bit frames: upload (1/8 of the bytes), then convertTo(CV_64FC1, alpha, beta) on the device
             unsigned char* d_raw = (unsigned char*)(base + in_bytes + out_bytes + st_bytes);
             if (step_bytes == (size_t)width && frame_stride_bytes == plane8) {
+                // the caller's last frame ends after width*height bytes, not after a padded plane
                 OF_CUDA(ctx, cudaMemcpyAsync(d_raw + k0 * plane8, src + (size_t)k0 * frame_stride_bytes,
-                                             plane8 * (np + 1 - k0), cudaMemcpyHostToDevice, ctx->copy_stream));
+                                             plane8 * (np - k0) + (size_t)width * height, cudaMemcpyHostToDevice,
+                                             ctx->copy_stream));
             } else {
                 for (int k = k0; k <= np; ++k)
                     OF_CUDA(ctx, cudaMemcpy2DAsync(d_raw + k * plane8, width, src + (size_t)k * frame_stride_bytes,
@@ -888,7 +925,7 @@ static of_status stream_impl(of_ctx* ctx, const void* frames, size_t esz, double
                                                ctx->copy_stream, &ctx->launches));
         } else if (dense_in) {
             OF_CUDA(ctx, cudaMemcpyAsync((char*)d_in + k0 * plane, src + (size_t)k0 * frame_stride_bytes,
-                                         plane * (np + 1 - k0), cudaMemcpyHostToDevice, ctx->copy_stream));
+                                         plane * (np - k0) + rowb * height, cudaMemcpyHostToDevice, ctx->copy_stream));
         } else {
             for (int k = k0; k <= np; ++k)
                 OF_CUDA(ctx, cudaMemcpy2DAsync((char*)d_in + k * plane, pitch * 8, src + (size_t)k * frame_stride_bytes,
@@ -909,8 +946,9 @@ static of_status stream_impl(of_ctx* ctx, const void* frames, size_t esz, double
             char* hu = (char*)u + (size_t)p0 * uv_pair_stride_bytes;
             char* hv = (char*)v + (size_t)p0 * uv_pair_stride_bytes;
             if (dense_out && uv_pair_stride_bytes == plane) {
-                OF_CUDA(ctx, cudaMemcpyAsync(hu, d_u, plane * np, cudaMemcpyDeviceToHost, ctx->down_stream));
-                OF_CUDA(ctx, cudaMemcpyAsync(hv, d_v, plane * np, cudaMemcpyDeviceToHost, ctx->down_stream));
+                const size_t nb = plane * (np - 1) + rowb * height;      // the last plane ends at its last pixel
+                OF_CUDA(ctx, cudaMemcpyAsync(hu, d_u, nb, cudaMemcpyDeviceToHost, ctx->down_stream));
+                OF_CUDA(ctx, cudaMemcpyAsync(hv, d_v, nb, cudaMemcpyDeviceToHost, ctx->down_stream));
             } else {
                 for (int k = 0; k < np; ++k) {
                     OF_CUDA(ctx, cudaMemcpy2DAsync(hu + (size_t)k * uv_pair_stride_bytes, uv_step_bytes,

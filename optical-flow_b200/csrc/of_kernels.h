@@ -4,6 +4,8 @@
 #include <cuda_runtime.h>
 #include <stddef.h>
 
+#include <atomic>
+
 #include "../../include/of_b200.h"
 
 namespace ofb {
@@ -81,6 +83,38 @@ struct LiveDiffArgs {         // live-loop pre-processing :800-813 (live_pre.cu)
     double* out;
     size_t out_pitch;         // doubles
 };
+
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a per-device attribute, and one process may drive
+// several devices from several threads (one context per device): remember the opt-in per device.
+struct SmemOptIn {
+    std::atomic<unsigned long long> done{0};      // bit d: set on device d (devices >= 64: set every time)
+    cudaError_t ensure(const void* func, size_t bytes)
+    {
+        int dev = 0;
+        cudaError_t e = cudaGetDevice(&dev);
+        if (e != cudaSuccess) return e;
+        if (dev < 64 && ((done.load(std::memory_order_acquire) >> dev) & 1ull)) return cudaSuccess;
+        e = cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+        if (e == cudaSuccess && dev < 64) done.fetch_or(1ull << dev, std::memory_order_release);
+        return e;
+    }
+};
+
+// Number of SMs of the current device (cached per device).
+inline int current_sm_count()
+{
+    static std::atomic<int> cache[64];
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return 148;
+    if (dev < 64) {
+        const int c = cache[dev].load(std::memory_order_relaxed);
+        if (c > 0) return c;
+    }
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+    if (dev < 64) cache[dev].store(n, std::memory_order_relaxed);
+    return n;
+}
 
 // Each returns the CUDA error of the launch and adds the number of kernels it launched
 // to *launches.

@@ -230,7 +230,7 @@ cudaError_t launch_pyr_down(const PyrDownArgs& a, cudaStream_t s, unsigned long 
     if ((a.w & 1) == 0 && a.w >= 4 && (((uintptr_t)a.src | (a.src_pitch * 8) | (a.src_img_stride * 8)) & 15) == 0) {
         const int strips = (ow + PDF_COLS - 1) / PDF_COLS;
         int rows = 64;
-        while (rows > 16 && (long)strips * ((oh + rows - 1) / rows) * a.n_images < 148L * 16) rows /= 2;
+        while (rows > 16 && (long)strips * ((oh + rows - 1) / rows) * a.n_images < (long)current_sm_count() * 16) rows /= 2;
         dim3 grid(strips, (oh + rows - 1) / rows, a.n_images);
         pyr_down_fast_kernel<<<grid, PD_NT, 0, s>>>(a, rows);
         if (launches) *launches += 1;
@@ -240,7 +240,7 @@ cudaError_t launch_pyr_down(const PyrDownArgs& a, cudaStream_t s, unsigned long 
     const int strips = (ow + PD_NT - 1) / PD_NT;
     // rows per CTA: long enough to amortise the 3 warm-up rows, short enough to fill the GPU
     int rows = 64;
-    while (rows > 16 && (long)strips * ((oh + rows - 1) / rows) * a.n_images < 148L * 12) rows /= 2;
+    while (rows > 16 && (long)strips * ((oh + rows - 1) / rows) * a.n_images < (long)current_sm_count() * 12) rows /= 2;
     dim3 grid(strips, (oh + rows - 1) / rows, a.n_images);
     pyr_down_kernel<<<grid, PD_NT, 0, s>>>(a, rows);
     if (launches) *launches += 1;

@@ -83,10 +83,10 @@ def test_random_inputs_vs_oracle(ofb, c_oracle, shape, r):
     check(got, c_oracle.coarse_to_fine(a, b, L, r, want_mask=True), r, "rand %s r=%d" % (shape, r))
 
 
-@pytest.mark.parametrize("variant", ["tile", "strip", "phase"])
+@pytest.mark.parametrize("variant", ["tile", "phase"])
 @pytest.mark.parametrize("r", [2, 5, 7])
 def test_every_level_kernel_vs_oracle(ofb, c_oracle, monkeypatch, variant, r):
-    """The library picks the level kernel itself (phase, else strip, else tile); OF_B200_VARIANT,
+    """The library picks the level kernel itself (phase, else tile); OF_B200_VARIANT,
     read when a context is created, pins one so that the fallbacks stay covered."""
     monkeypatch.setenv("OF_B200_VARIANT", variant)
     for h, w, L in [(120, 200, 4), (300, 34, 2), (96, 260, 3)]:
