@@ -1,4 +1,4 @@
-// Phase-synchronous fused pyramid-level kernel (throughput path), window radius R = 2..7.
+// Phase-synchronous fused pyramid-level kernel (throughput path), window radius R = 1..7.
 //
 // One launch = one pyramid level of every pair of the batch, everything the reference does
 // between two levels (ParallelVideoPyr.cpp:610-703) plus the single-level LK (:327-542):
@@ -11,7 +11,10 @@
 // light per-element job, so latency is hidden by thread count instead of by deep per-warp
 // pipelines:
 //
-//   P0  horizontal pass of cv::pyrUp for the coarse-flow rows the next step needs     -> HR ring
+//   P0  coarse-flow rows the next step needs: one thread hands the rows to the copy engine
+//       (cp.async.bulk.tensor, one box of 66 coarse columns per row and plane, zero-filled
+//       outside the plane, completion on an mbarrier) while the block runs P2; afterwards
+//       the horizontal pass of cv::pyrUp turns them into fine columns                  -> HR ring
 //   P1  one warp per fine row, a lane takes columns lane + 32 i: vertical pass of pyrUp,
 //       float32 maps, 8 coalesced gathers per pixel, two blends                       -> AB
 //       (the upsampled flow of output pixels is parked in u, v for the epilogue)
@@ -19,7 +22,8 @@
 //       frames, five products, horizontal window sums in registers + shuffles        -> PROD
 //   P3  per (channel, column pair): vertical window sums, van Herk / Gil-Werman; suffix
 //       sums of the previous block in shared memory, this block's rows in registers  -> PROD, VS
-//   P4  per (row, column pair): guarded solve, += parked up-flow, stores, mask, statistics
+//   P4  one warp per output row, a lane takes 4 columns: guarded solve, += parked up-flow,
+//       stores, mask, statistics
 //
 // The step loop at the bottom of the file overlaps the latency-bound P1 of the next step with
 // P3 and P4 of the current one (see the schedule comment there).
@@ -36,12 +40,25 @@
 // in L2 (a step's rows are re-read within microseconds).
 #include "lk_common.cuh"
 #include "of_kernels.h"
+#include "tma.cuh"
+#include "tmem.cuh"
+
+#include <string.h>
 
 namespace ofb {
 
 #ifdef PH_PROF
 // Development aid: per-warp cycle totals of the first CTA, by region of the step loop.
 __device__ unsigned long long g_phase_prof[32 * 8];
+#ifdef PH_PROF1
+__device__ unsigned long long g_p1_prof[32 * 8];
+#define P1_MARK(slot)                                                            \
+    do {                                                                         \
+        const long long t_now = clock64();                                       \
+        p1_acc[slot] += t_now - p1_t;                                            \
+        p1_t = t_now;                                                            \
+    } while (0)
+#endif
 #define PH_MARK(slot)                                                            \
     do {                                                                         \
         const long long t_now = clock64();                                       \
@@ -51,19 +68,24 @@ __device__ unsigned long long g_phase_prof[32 * 8];
 #else
 #define PH_MARK(slot) do { } while (0)
 #endif
+#ifndef P1_MARK
+#define P1_MARK(slot) do { } while (0)
+#endif
 
 namespace {
 
-#ifndef PH_IDLE16
-#define PH_IDLE16 80             // head start (in 1/16 chunks of 32 P4 tasks) of a V warp without a P1 row ...
-#define PH_O16 18                // ... and of an O warp, over a V warp with a P1 row
-#endif
 constexpr int PH_NT = 512;       // threads per CTA (16 warps; a warp = one row of 32 quads)
 constexpr int PH_NW = PH_NT / 32;
 constexpr int PH_PC = 128;       // product columns per strip = 32 lanes x 4 columns
 constexpr int AB_HALF = 72;      // warped-frame rows: lo pairs [0,64), hi pairs [72,136)
 constexpr int AB_PITCH = 136;
-constexpr int HR_RING = 16;     // coarse-flow rows kept in shared memory: row k lives in slot (k + 2) & 15
+constexpr int HR_RING = 16;      // upsampled coarse-flow rows kept in shared memory: row k lives in slot (k + 2) & 15,
+                                 // element (column X, plane p) at (slot * 128 + X) * 2 + p  (u, v interleaved)
+constexpr int CR_W = 68;         // raw coarse columns landed per strip: 64 + one neighbour on either side, starting
+                                 // one column further left (the copy engine wants a 16-byte aligned box start)
+constexpr int CR_PITCH = 80;     // doubles between the rows of the landing buffer: 640 B = 5 x 128 B (TMA alignment)
+
+constexpr int al16(int d) { return (d + 15) / 16 * 16; }
 
 template <int R>
 struct PhaseCfg {
@@ -80,9 +102,19 @@ struct PhaseCfg {
     static constexpr int PROD_D = WIN * 5 * PPITCH;
     static constexpr int AB_D = AB_ROWS * 2 * AB_PITCH;
     static constexpr int HR_D = HR_RING * 2 * PH_PC;
-    static constexpr int VS_D = 2 * R * 5 * PPITCH;   // suffix sums of the previous vertical block
-    static constexpr size_t SMEM_BYTES = (size_t)(PROD_D + AB_D + HR_D + VS_D) * 8;
+    static constexpr int CR_D = HR_ROWS * 2 * CR_PITCH;   // landing buffer of the coarse rows (raw)
+    // offsets in doubles; the landing buffer must be 128-byte aligned
+    static constexpr int O_AB = al16(PROD_D);
+    static constexpr int O_HR = O_AB + al16(AB_D);
+    static constexpr int O_CR = O_HR + HR_D;
+    static constexpr int O_BAR = O_CR + CR_D;              // mbarrier (8 bytes) + TMEM base address (4 bytes)
+    // Tensor memory: a P3 thread keeps the 2R raw rows 1 .. 2R of the previous vertical block of its
+    // (channel, column pair) there, 2R x 2 doubles = 8R columns; a column slot of 64 per warp
+    static constexpr int TM_SLOT = 64;
+    static constexpr int TM_COLS = 256;
+    static constexpr size_t SMEM_BYTES = (size_t)(O_BAR + 2) * 8;
     static constexpr int VPAIRS = 2 * OUT_LANES;      // column pairs per channel in P3
+    static constexpr int NT = PH_NT;
 };
 
 // R = 1 (the reference's own 3x3 window, get_Sum9 :114-160): the nine terms are summed in the
@@ -101,14 +133,18 @@ struct PhaseCfg<1> {
     static constexpr int WIN = PH1_WIN;               // rows per step
     static constexpr int CTAS = PH1_CTAS;             // CTAs per SM
     static constexpr int NT = 32 * (WIN + 1);         // one warp per row of P1 (+ the row above the first step)
-    static constexpr int UPK = ((WIN + 1) / 2 + 3) * PH_PC / NT + 1;
     static constexpr int AB_ROWS = WIN + 1;
     static constexpr int HR_ROWS = (WIN + 1) / 2 + 3;
     static constexpr int PR_ROWS = WIN + 2;           // product-row ring
     static constexpr int PROD_D = PR_ROWS * 5 * 136;
     static constexpr int AB_D = AB_ROWS * 2 * 136;
     static constexpr int HR_D = HR_RING * 2 * PH_PC;
-    static constexpr size_t SMEM_BYTES = (size_t)(PROD_D + AB_D + HR_D) * 8;
+    static constexpr int CR_D = HR_ROWS * 2 * CR_PITCH;
+    static constexpr int O_AB = al16(PROD_D);
+    static constexpr int O_HR = O_AB + al16(AB_D);
+    static constexpr int O_CR = O_HR + HR_D;
+    static constexpr int O_BAR = O_CR + CR_D;
+    static constexpr size_t SMEM_BYTES = (size_t)(O_BAR + 2) * 8;
 };
 
 // Shared-memory rows that are read four columns per lane are "pair-split": columns 4j, 4j+1 of
@@ -135,70 +171,59 @@ struct PGeo {
     int y0, y1;       // output rows [y0, y1)
     bool has_coarse;
     bool edge;        // strip reaches outside the image on the left or right
-    bool vec_img, vec_uv, vec_c;   // 16-byte alignment of the image / flow / coarse-flow rows
 };
 
 // Position of strip column X inside a warped-frame row.
 __device__ __forceinline__ int ppos(int X) { return ((X & 2) ? AB_HALF : 0) + 2 * (X >> 2) + (X & 1); }
 
 // ------------------------------------------------------------------------------ P0
-// Horizontal pass of cv::pyrUp (:646-647) of coarse rows rho(ka) .. rho(ka + nk - 1), both
-// flow planes, for the strip's 128 fine columns (plain layout); task = (row, plane, coarse
-// column j) -> fine columns 2j, 2j+1.  Columns outside the image hold 0.  Split in two so that
-// the global loads are in flight while the thread does other work: issue() starts the loads of
-// the thread's (at most UP_K) tasks, finish() forms the rows and stores them.
-template <int UP_K>
-struct UpPreT { double sm1[UP_K], s0[UP_K], s1[UP_K]; };
-using UpPre = UpPreT<3>;
-
-template <int HR_ROWS, int PH_NT = 512, int UP_K = 3>
-__device__ __forceinline__ void up_rows_issue(const LevelArgs& a, const PGeo& g, const double* __restrict__ cu,
-                                              const double* __restrict__ cv, int ka, int nk, UpPreT<UP_K>& q)
+// Coarse-flow rows rho(k_from) .. rho(k_from + n_new - 1) (cv::pyrUp's row map, :646-647) of both
+// planes -> landing buffer, by the copy engine: one box of CR_W columns starting two coarse columns
+// left of the strip (an even column: FP64 boxes must start 16-byte aligned) per row and plane; columns
+// outside the plane arrive as 0.  Called by one thread.
+__device__ __forceinline__ void up_rows_issue(const CUtensorMap* tmu, const CUtensorMap* tmv, int j0, int hc, int pair,
+                                              int k_from, int n_new, double* s_cr, uint64_t* bar)
 {
-    static_assert(UP_K * PH_NT >= HR_ROWS * PH_PC && HR_ROWS <= HR_RING, "UP_K too small");
-    const int wc = a.wc, hc = a.hc;
-    const int j = (g.c0 >> 1) + (threadIdx.x & 63);
-    const int p = (threadIdx.x >> 6) & 1;
-    const double* plane = p ? cv : cu;
-    const bool interior = j >= 1 && j + 1 < wc;
-#pragma unroll
-    for (int k = 0; k < UP_K; ++k) {
-        const int r = (threadIdx.x >> 7) + k * (PH_NT / PH_PC);
-        q.sm1[k] = q.s0[k] = q.s1[k] = 0.0;
-        if (r < nk && interior) {
-            const double* row = plane + (size_t)pyrup_rho(ka + r, hc) * a.c_pitch + j;
-            q.sm1[k] = __ldg(row - 1);
-            q.s0[k] = __ldg(row);
-            q.s1[k] = __ldg(row + 1);
-        }
+    mbar_arrive_expect_tx(bar, (uint32_t)n_new * (uint32_t)(2 * CR_W * sizeof(double)));
+    for (int r = 0; r < n_new; ++r) {
+        const int row = pyrup_rho(k_from + r, hc);
+        tma_load_3d(s_cr + (2 * r) * CR_PITCH, tmu, j0, row, pair, bar);
+        tma_load_3d(s_cr + (2 * r + 1) * CR_PITCH, tmv, j0, row, pair, bar);
     }
 }
 
-template <int PH_NT = 512, int UP_K = 3>
-__device__ __forceinline__ void up_rows_finish(const LevelArgs& a, const PGeo& g, const double* __restrict__ cu,
-                                               const double* __restrict__ cv, int ka, int nk, const UpPreT<UP_K>& q,
-                                               double* s_hr)
+// Horizontal pass of cv::pyrUp (:646-647) over the landed rows -> HR ring; task = (row, coarse
+// column j) -> fine columns 2j, 2j+1 of both planes.  Fine columns outside the image hold 0.
+template <int NT>
+__device__ __forceinline__ void up_rows_hpass(const PGeo& g, int wc, int k_from, int n_new, const double* s_cr,
+                                              double* s_hr)
 {
-    const int wc = a.wc, hc = a.hc;
     const int jl = threadIdx.x & 63;
-    const int j = (g.c0 >> 1) + jl;
-    const int p = (threadIdx.x >> 6) & 1;
-    const bool interior = j >= 1 && j + 1 < wc;
-#pragma unroll
-    for (int k = 0; k < UP_K; ++k) {
-        const int r = (threadIdx.x >> 7) + k * (PH_NT / PH_PC);
-        if (r >= nk) continue;
-        double e = dadd(dadd(q.sm1[k], dmul(q.s0[k], 6.0)), q.s1[k]);
-        double o = dmul(dadd(q.s0[k], q.s1[k]), 4.0);
-        if (!interior) {
-            e = o = 0.0;
-            if ((unsigned)j < (unsigned)wc) {                // image border: cv::pyrUp's edge formulas
-                const double* row = (p ? cv : cu) + (size_t)pyrup_rho(ka + r, hc) * a.c_pitch;
-                e = pyrup_row(row, 0, 2 * j, wc);
-                o = pyrup_row(row, 0, 2 * j + 1, wc);
-            }
+    const int j0 = (g.c0 >> 1) - 2;                     // coarse column of landing column 0
+    const int j = j0 + 2 + jl;
+    const bool border = (unsigned)(j - 1) >= (unsigned)(wc - 2);      // j <= 0 or j >= wc - 1
+    for (int r = threadIdx.x >> 6; r < n_new; r += NT / 64) {
+        const double* cu = s_cr + (2 * r) * CR_PITCH + jl + 1;       // cu[0] = column j - 1
+        const double* cv = cu + CR_PITCH;
+        double eu, ou, ev, ov;
+        if (!border) {
+            const double um = cu[0], u0 = cu[1], u1 = cu[2];
+            const double vm = cv[0], v0 = cv[1], v1 = cv[2];
+            eu = dadd(dadd(um, dmul(u0, 6.0)), u1);
+            ou = dmul(dadd(u0, u1), 4.0);
+            ev = dadd(dadd(vm, dmul(v0, 6.0)), v1);
+            ov = dmul(dadd(v0, v1), 4.0);
+        } else if ((unsigned)j < (unsigned)wc) {                     // image border: cv::pyrUp's edge formulas
+            eu = pyrup_row(cu - jl - 1, j0, 2 * j, wc);
+            ou = pyrup_row(cu - jl - 1, j0, 2 * j + 1, wc);
+            ev = pyrup_row(cv - jl - 1, j0, 2 * j, wc);
+            ov = pyrup_row(cv - jl - 1, j0, 2 * j + 1, wc);
+        } else {
+            eu = ou = ev = ov = 0.0;
         }
-        sts2(s_hr + ((((ka + r + 2) & (HR_RING - 1)) * 2 + p) * PH_PC) + 2 * jl, e, o);
+        double* d = s_hr + ((((k_from + r + 2) & (HR_RING - 1)) * PH_PC) + 2 * jl) * 2;
+        sts2(d, eu, ev);
+        sts2(d + 2, ou, ov);
     }
 }
 
@@ -208,6 +233,12 @@ __device__ __forceinline__ void up_rows_finish(const LevelArgs& a, const PGeo& g
 // ...; one warp per row, a lane takes the columns lane + 32 i so
 // that every gather instruction of the warp reads 32 neighbouring pixels.  Row -1 is the
 // reflect-101 row above row 0 (image row 1); other rows outside the image are never read.
+//
+// Map arithmetic (:667-684 and cv::remap's fixed point): the reference forms m = x + f / 2 in float32
+// and remap rounds m * 32 to an integer.  Scaling by 32 commutes with the float32 rounding of the
+// sum, so s = rint(32 x + 16 f) is the same integer with two instructions less per coordinate
+// (32 x is exact; the only inexact cases are |m| below 2^-120, where both give 0).  A non-finite
+// or huge flow is clamped to 3e38: the tap then lies outside the image like the reference's.
 template <int R>
 __device__ __forceinline__ void phase_remap(const LevelArgs& a, const PGeo& g, const double* __restrict__ A,
                                             const double* __restrict__ B, double* __restrict__ U,
@@ -218,6 +249,11 @@ __device__ __forceinline__ void phase_remap(const LevelArgs& a, const PGeo& g, c
     const int W = g.W, H = g.H;
     const int pitch = (int)a.img_pitch;
     const int lane = threadIdx.x & 31;
+    const int x0 = g.c0 + lane;
+#ifdef PH_PROF1
+    long long p1_acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    long long p1_t = clock64();
+#endif
     for (int r = r_first; r <= C::WIN; r += r_step) {
         const int vy = vy0 + r - 1;
         int yy = vy;
@@ -225,118 +261,200 @@ __device__ __forceinline__ void phase_remap(const LevelArgs& a, const PGeo& g, c
         else if ((unsigned)vy >= (unsigned)H) continue;
         int slot = sb + r;
         if (slot >= C::AB_ROWS) slot -= C::AB_ROWS;
-        double* dst = s_ab + slot * (2 * AB_PITCH);
+        double* dst = s_ab + slot * (2 * AB_PITCH) + ppos(lane);       // column lane + 32 i at dst[16 i]
+        P1_MARK(0);
         double va[4] = {0.0, 0.0, 0.0, 0.0}, vb[4] = {0.0, 0.0, 0.0, 0.0};
-        const int x0 = g.c0 + lane;
-        unsigned inm = 0;                                    // columns of this lane inside the image
-#pragma unroll
-        for (int i = 0; i < 4; ++i) inm |= (unsigned)(x0 + 32 * i) < (unsigned)W ? (1u << i) : 0u;
 #ifdef PH_KNOCK_REMAP
         if (false) {
 #else
         if (g.has_coarse) {
 #endif
-            // vertical pass of cv::pyrUp from the rows of P0
+            // vertical pass of cv::pyrUp from the rows of P0 (u, v interleaved: one 16-byte load per row)
             const int k = yy >> 1;
-            const double* hm = s_hr + (((k + 1) & (HR_RING - 1)) * 2) * PH_PC + lane;   // row k-1, plane u
-            const double* h0 = s_hr + (((k + 2) & (HR_RING - 1)) * 2) * PH_PC + lane;   // row k
-            const double* hp = s_hr + (((k + 3) & (HR_RING - 1)) * 2) * PH_PC + lane;   // row k+1
+            const double* h0 = s_hr + ((((k + 2) & (HR_RING - 1)) * PH_PC) + lane) * 2;   // row k
+            const double* hp = s_hr + ((((k + 3) & (HR_RING - 1)) * PH_PC) + lane) * 2;   // row k+1
             double upu[4], upv[4];
             if (yy & 1) {
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
+                    const double2 c = lds2(h0 + 64 * i), p = lds2(hp + 64 * i);
                     // (a * 4) / 64 == a / 16: both scalings are exact
-                    upu[i] = dmul(dadd(h0[32 * i], hp[32 * i]), 1.0 / 16.0);
-                    upv[i] = dmul(dadd(h0[PH_PC + 32 * i], hp[PH_PC + 32 * i]), 1.0 / 16.0);
+                    upu[i] = dmul(dadd(c.x, p.x), 1.0 / 16.0);
+                    upv[i] = dmul(dadd(c.y, p.y), 1.0 / 16.0);
                 }
             } else {
+                const double* hm = s_hr + ((((k + 1) & (HR_RING - 1)) * PH_PC) + lane) * 2;   // row k-1
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
-                    upu[i] = dmul(dadd(dadd(hm[32 * i], dmul(h0[32 * i], 6.0)), hp[32 * i]), 1.0 / 64.0);
-                    upv[i] = dmul(dadd(dadd(hm[PH_PC + 32 * i], dmul(h0[PH_PC + 32 * i], 6.0)), hp[PH_PC + 32 * i]),
-                                  1.0 / 64.0);
+                    const double2 m = lds2(hm + 64 * i), c = lds2(h0 + 64 * i), p = lds2(hp + 64 * i);
+                    upu[i] = dmul(dadd(dadd(m.x, dmul(c.x, 6.0)), p.x), 1.0 / 64.0);
+                    upv[i] = dmul(dadd(dadd(m.y, dmul(c.y, 6.0)), p.y), 1.0 / 64.0);
                 }
             }
+            P1_MARK(1);
             // park the upsampled flow of output pixels for the epilogue (tmpu += upu, :634-637)
+#ifdef PH_KNOCK_PARK
+            if (false) {
+#else
             if (vy == yy && vy >= g.y0 && vy < g.y1) {
+#endif
                 const int off = vy * (int)a.uv_pitch + x0;
                 double* pu = U + off;
                 double* pv = V + off;
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
-                    const int X = lane + 32 * i;
-                    if (X >= 4 * C::HL && X < 4 * C::HL + C::OUT_COLS && ((inm >> i) & 1u)) {
+                    bool ok = true;
+                    if (i == 0) ok = lane >= 4 * C::HL;
+                    if (i == 3) ok = lane < 4 * C::HL + C::OUT_COLS - 96;
+                    if (g.edge) ok = ok && (unsigned)(x0 + 32 * i) < (unsigned)W;
+                    if (ok) {
                         pu[32 * i] = upu[i];
                         pv[32 * i] = upv[i];
                     }
                 }
             }
-            float hu4[4], hv4[4];                            // half flow, float32 (map build :667-684)
-            unsigned finite = 0;
+            P1_MARK(2);
+            float hu[4], hv[4];                              // 32 * (f / 2), float32
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
-                hu4[i] = __fmul_rn(__double2float_rn(upu[i]), 0.5f);          // == f / 2 exactly
-                hv4[i] = __fmul_rn(__double2float_rn(upv[i]), 0.5f);
-                finite |= (fabsf(hu4[i]) + fabsf(hv4[i]) < __int_as_float(0x7f800000)) ? (1u << i) : 0u;
+                hu[i] = fminf(__fmul_rn(__double2float_rn(upu[i]), 16.0f), 3.0e38f);
+                hv[i] = fminf(__fmul_rn(__double2float_rn(upv[i]), 16.0f), 3.0e38f);
             }
-            const float xf = (float)x0, yf = (float)yy;
-            // frame 1 is sampled at (x + hu, y + hv), frame 2 at (x - hu, y - hv)
+            const float xf = (float)(32 * x0), yf = (float)(32 * yy);
+            // frame 1 is sampled at (x + f.x / 2, y + f.y / 2), frame 2 at (x - f.x / 2, y - f.y / 2)
+#ifndef PH_P1_SEQ
+            // both frames' 32 gathers in flight before the first blend (measured: level 0 0.976 -> 0.910 ms)
+            int off[2][4], fr[2][4];
+            unsigned out = 0;
+#pragma unroll
+            for (int f = 0; f < 2; ++f)
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const float xi = __fadd_rn(xf, 1024.0f * (float)i);
+                    const int sx = __float2int_rn(f ? __fsub_rn(xi, hu[i]) : __fadd_rn(xi, hu[i]));
+                    const int sy = __float2int_rn(f ? __fsub_rn(yf, hv[i]) : __fadd_rn(yf, hv[i]));
+                    const int ix = sx >> 5, iy = sy >> 5;
+                    const bool interior = (unsigned)ix < (unsigned)(W - 1) && (unsigned)iy < (unsigned)(H - 1);
+                    off[f][i] = interior ? iy * pitch + ix : 0;
+                    if (!interior) out |= 1u << (4 * f + i);
+                    fr[f][i] = (sx & 31) | ((sy & 31) << 8);
+                }
+            double sv[2][4][4];
+#pragma unroll
+            for (int f = 0; f < 2; ++f)
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const double* pa = (f ? B : A) + (unsigned)off[f][i];
+                    sv[f][i][0] = __ldg(pa); sv[f][i][1] = __ldg(pa + 1);
+                    sv[f][i][2] = __ldg(pa + pitch); sv[f][i][3] = __ldg(pa + pitch + 1);
+                }
 #pragma unroll
             for (int f = 0; f < 2; ++f) {
-                const double* __restrict__ F = f ? B : A;
-                Tap tp[4];
-                unsigned all_in = 0x10000;
-#pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    const float xi = xf + (float)(32 * i);
-                    const float mx = f ? __fsub_rn(xi, hu4[i]) : __fadd_rn(xi, hu4[i]);
-                    const float my = f ? __fsub_rn(yf, hv4[i]) : __fadd_rn(yf, hv4[i]);
-                    tp[i] = make_tap(mx, my, W, H, pitch, (finite >> i) & 1u);
-                    all_in &= tp[i].fr | (((inm >> i) & 1u) ? 0u : 0x10000u);
-                }
-                double sv[4][4];                             // 16 gathers, issued back to back
-#pragma unroll
-                for (int i = 0; i < 4; ++i) {
-#ifdef PH_KNOCK_L1
-                    const double* pa = F + ((unsigned)tp[i].off & 1023u);
-#else
-                    const double* pa = F + (unsigned)tp[i].off;     // off >= 0: one IMAD.WIDE.U32
-#endif
-                    sv[i][0] = __ldg(pa); sv[i][1] = __ldg(pa + 1);
-                    sv[i][2] = __ldg(pa + pitch); sv[i][3] = __ldg(pa + pitch + 1);
-                }
                 double* v = f ? vb : va;
 #pragma unroll
-                for (int i = 0; i < 4; ++i)
-                    v[i] = R == 1 ? blend4_exact(sv[i][0], sv[i][1], sv[i][2], sv[i][3], tp[i].fr)
-                                  : blend4(sv[i][0], sv[i][1], sv[i][2], sv[i][3], tp[i].fr);
-                if (!all_in) {                               // rare: a tap outside the image, non-finite map
+                for (int i = 0; i < 4; ++i) {
+                    const int ax = fr[f][i] & 31, ay = fr[f][i] >> 8;
+                    v[i] = R == 1 ? blend4_exact(sv[f][i][0], sv[f][i][1], sv[f][i][2], sv[f][i][3], ax, ay)
+                                  : blend4(sv[f][i][0], sv[f][i][1], sv[f][i][2], sv[f][i][3], ax, ay);
+                }
+            }
+            if (out) {                                       // rare: a tap outside the image, non-finite flow
+#pragma unroll
+                for (int f = 0; f < 2; ++f) {
+                    const double* __restrict__ F = f ? B : A;
+                    double* v = f ? vb : va;
 #pragma unroll
                     for (int i = 0; i < 4; ++i) {
-                        if (!(tp[i].fr & 0x10000) && ((inm >> i) & 1u)) {
-                            const float xi = xf + (float)(32 * i);
-                            const float mx = f ? __fsub_rn(xi, hu4[i]) : __fadd_rn(xi, hu4[i]);
-                            const float my = f ? __fsub_rn(yf, hv4[i]) : __fadd_rn(yf, hv4[i]);
+                        if (((out >> (4 * f + i)) & 1u) && (unsigned)(x0 + 32 * i) < (unsigned)W) {
+                            const float xr = (float)(x0 + 32 * i), yr = (float)yy;
+                            const float hx = __fmul_rn(hu[i], 1.0f / 32.0f), hy = __fmul_rn(hv[i], 1.0f / 32.0f);
+                            const float mx = f ? __fsub_rn(xr, hx) : __fadd_rn(xr, hx);
+                            const float my = f ? __fsub_rn(yr, hy) : __fadd_rn(yr, hy);
                             v[i] = remap_tap4(F, a.img_pitch, W, H, mx, my);
                         }
                     }
                 }
             }
+#else
+#pragma unroll
+            for (int f = 0; f < 2; ++f) {
+                const double* __restrict__ F = f ? B : A;
+                int off[4], ax[4], ay[4];
+                unsigned out = 0;                            // taps not inside the image
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const float xi = __fadd_rn(xf, 1024.0f * (float)i);
+                    const int sx = __float2int_rn(f ? __fsub_rn(xi, hu[i]) : __fadd_rn(xi, hu[i]));
+                    const int sy = __float2int_rn(f ? __fsub_rn(yf, hv[i]) : __fadd_rn(yf, hv[i]));
+                    const int ix = sx >> 5, iy = sy >> 5;
+                    const bool interior = (unsigned)ix < (unsigned)(W - 1) && (unsigned)iy < (unsigned)(H - 1);
+                    off[i] = interior ? iy * pitch + ix : 0;
+                    if (!interior) out |= 1u << i;
+                    ax[i] = sx & 31;
+                    ay[i] = sy & 31;
+                }
+                double sv[4][4];                             // 16 gathers, issued back to back
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+#ifdef PH_KNOCK_L1
+                    const double* pa = F + ((unsigned)off[i] & 1023u);
+#else
+                    const double* pa = F + (unsigned)off[i];
+#endif
+                    sv[i][0] = __ldg(pa); sv[i][1] = __ldg(pa + 1);
+                    sv[i][2] = __ldg(pa + pitch); sv[i][3] = __ldg(pa + pitch + 1);
+                }
+                double* v = f ? vb : va;
+                P1_MARK(3 + 2 * f);
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+#ifdef PH_KNOCK_BLEND
+                    v[i] = dadd(dadd(sv[i][0], sv[i][1]), dadd(sv[i][2], __hiloint2double(sv[i][3] > 0.5 ? ax[i] : ay[i], 0)));
+#else
+                    v[i] = R == 1 ? blend4_exact(sv[i][0], sv[i][1], sv[i][2], sv[i][3], ax[i], ay[i])
+                                  : blend4(sv[i][0], sv[i][1], sv[i][2], sv[i][3], ax[i], ay[i]);
+#endif
+                P1_MARK(4 + 2 * f);
+                if (out) {                                   // rare: a tap outside the image, non-finite flow
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        if (((out >> i) & 1u) && (unsigned)(x0 + 32 * i) < (unsigned)W) {
+                            const float xr = (float)(x0 + 32 * i), yr = (float)yy;
+                            const float hx = __fmul_rn(hu[i], 1.0f / 32.0f), hy = __fmul_rn(hv[i], 1.0f / 32.0f);
+                            const float mx = f ? __fsub_rn(xr, hx) : __fadd_rn(xr, hx);
+                            const float my = f ? __fsub_rn(yr, hy) : __fadd_rn(yr, hy);
+                            v[i] = remap_tap4(F, a.img_pitch, W, H, mx, my);
+                        }
+                    }
+                }
+            }
+#endif
         } else {
             const double* pa = A + (size_t)yy * a.img_pitch + x0;
             const double* pb = B + (size_t)yy * a.img_pitch + x0;
 #pragma unroll
             for (int i = 0; i < 4; ++i)
-                if ((inm >> i) & 1u) { va[i] = __ldg(pa + 32 * i); vb[i] = __ldg(pb + 32 * i); }
+                if ((unsigned)(x0 + 32 * i) < (unsigned)W) { va[i] = __ldg(pa + 32 * i); vb[i] = __ldg(pb + 32 * i); }
+        }
+        if (g.edge) {                                        // columns outside the image read as 0
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const bool in = (unsigned)(x0 + 32 * i) < (unsigned)W;
+                va[i] = in ? va[i] : 0.0;
+                vb[i] = in ? vb[i] : 0.0;
+            }
         }
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
-            const bool in = (inm >> i) & 1u;
-            const int q = ppos(lane + 32 * i);
-            dst[q] = in ? va[i] : 0.0;
-            dst[AB_PITCH + q] = in ? vb[i] : 0.0;
+            dst[16 * i] = va[i];
+            dst[AB_PITCH + 16 * i] = vb[i];
         }
+        P1_MARK(7);
     }
+#ifdef PH_PROF1
+    if (blockIdx.x == 1 && blockIdx.y == 0 && blockIdx.z == 0 && lane == 0 && W >= 1920)
+        for (int i = 0; i < 8; ++i) atomicAdd(&g_p1_prof[(threadIdx.x >> 5) * 8 + i], (unsigned long long)p1_acc[i]);
+#endif
 }
 
 // ------------------------------------------------------------------------------ P2
@@ -422,56 +540,67 @@ __device__ __forceinline__ void phase_products(const PGeo& g, int vy0, int sb, c
 // ------------------------------------------------------------------------------ P3
 // Vertical (2R+1)-row window sums of one (channel, column pair), in place.  van Herk /
 // Gil-Werman: the window of block row i is the suffix of the previous block from row i+1 plus
-// the prefix of this block up to row i.  vs[t] holds that suffix for row t+1 on entry; this
-// block's raw rows stay in registers and are turned into the next suffix sums at the end.
+// the prefix of this block up to row i.  The previous block's raw rows 1 .. 2R are the thread's
+// own state from the last step and live in tensor memory (taddr), not in shared memory: they are
+// loaded, turned into the suffix sums in registers, and this block's raw rows are stored back as
+// they are read.  Additions only, in the order  row(t+1) + (row(t+2) + ... ).
+// Warp-collective (tcgen05.ld / st): threads without a task run it with active = false.
 template <int R>
-__device__ __forceinline__ void phase_vertical(double* col, double* vs)
+__device__ __forceinline__ void phase_vertical(double* col, uint32_t taddr, bool active)
 {
     constexpr int WIN = 2 * R + 1;
     constexpr int ROW = 5 * PhaseCfg<R>::PPITCH;
-    double2 P = make_double2(0.0, 0.0);
-    double2 raw[2 * R];
+    double2 sf[2 * R];                                   // sf[t] = rows t+1 .. 2R of the previous block
+#pragma unroll
+    for (int c = 0; c < R; ++c) {
+        double t[4];
+        tmem_ld4(taddr + 8 * c, t);
+        sf[2 * c] = make_double2(t[0], t[1]);
+        sf[2 * c + 1] = make_double2(t[2], t[3]);
+    }
+    tmem_wait_ld();
+#pragma unroll
+    for (int t = 2 * R - 2; t >= 0; --t) {
+        sf[t].x = dadd(sf[t].x, sf[t + 1].x);
+        sf[t].y = dadd(sf[t].y, sf[t + 1].y);
+    }
+    double2 P = make_double2(0.0, 0.0), keep = P;
 #pragma unroll
     for (int i = 0; i < WIN; ++i) {
-        const double2 p = lds2(col + i * ROW);
+        const double2 p = lds2(col + i * ROW);            // threads without a task read column pair 0 and drop it
         if (i == 0) P = p;
         else { P.x = dadd(P.x, p.x); P.y = dadd(P.y, p.y); }
         double2 S = P;
         if (i < WIN - 1) {
-            const double2 sf = lds2(vs + i * ROW);
-            S.x = dadd(sf.x, P.x);
-            S.y = dadd(sf.y, P.y);
+            S.x = dadd(sf[i].x, P.x);
+            S.y = dadd(sf[i].y, P.y);
         }
-        sts2(col + i * ROW, S.x, S.y);
-        if (i >= 1) raw[i - 1] = p;
+        if (active) sts2(col + i * ROW, S.x, S.y);
+        if (i >= 1) {                                    // raw rows 1 .. 2R -> tensor memory, two rows per store
+            if (i & 1) keep = p;
+            else {
+                const double t[4] = {keep.x, keep.y, p.x, p.y};
+                tmem_st4(taddr + 8 * (i / 2 - 1), t);
+            }
+        }
     }
-    double2 acc = raw[2 * R - 1];
-    sts2(vs + (2 * R - 1) * ROW, acc.x, acc.y);
-#pragma unroll
-    for (int t = 2 * R - 2; t >= 0; --t) {
-        acc.x = dadd(raw[t].x, acc.x);
-        acc.y = dadd(raw[t].y, acc.y);
-        sts2(vs + t * ROW, acc.x, acc.y);
-    }
+    tmem_wait_st();
 }
 
 // ------------------------------------------------------------------------------ P4
 // Guarded 2x2 solve (:407-542), += upsampled coarse flow (:634-637), stores, mask, gesture
-// statistics (:845-873) of output rows y0 + m0 + i, i = i_lo .. i_hi-1; tasks (row, column pair)
-// t_begin, t_begin + nthr, ... < t_end of the (i_hi - i_lo) * OUT_COLS / 2 tasks.
+// statistics (:845-873).
 struct StatAcc { unsigned long long x, y, c; };
 
-// Solve + epilogue of output pixels (y, xb), (y, xb + 1) from their five window sums.
+// Solve + epilogue of output pixels (y, xb), (y, xb + 1) from their five window sums; the statistics
+// of the pair are added to the caller's per-row counters (sx: sum of the columns, sc: count).
 template <int R, bool VEC>
-__device__ __forceinline__ void solve_pair(const LevelArgs& a, const PGeo& g, double* __restrict__ U,
-                                           double* __restrict__ V, unsigned char* __restrict__ M, int y, int xb,
+__device__ __forceinline__ void solve_pair(const LevelArgs& a, const PGeo& g, double* __restrict__ pu,
+                                           double* __restrict__ pv, unsigned char* __restrict__ pm, bool yin, int xb,
                                            double2 sxx, double2 syy, double2 sxy, double2 sxt, double2 syt,
-                                           double det_eps, double mag2, StatAcc& st)
+                                           double det_eps, double mag2, unsigned& sx, unsigned& sc)
 {
-    const int W = g.W, H = g.H;
-    const int off = y * (int)a.uv_pitch + xb;            // < 2^31 (checked by the launcher)
-    double* pu = U + off;
-    double* pv = V + off;
+    const int W = g.W;
     double upu[2] = {0.0, 0.0}, upv[2] = {0.0, 0.0};
     if (g.has_coarse) {                                  // parked by P1 (same CTA, barriers between)
         if constexpr (VEC) {
@@ -481,7 +610,6 @@ __device__ __forceinline__ void solve_pair(const LevelArgs& a, const PGeo& g, do
             upu[0] = pu[0]; upu[1] = pu[1]; upv[0] = pv[0]; upv[1] = pv[1];
         }
     }
-    const bool yin = y >= R && y <= H - 1 - R;
     double lu[2], lv[2], nus[2], nvs[2], dets[2];
     unsigned okbits = 0;
     bool fast = true;
@@ -521,46 +649,50 @@ __device__ __forceinline__ void solve_pair(const LevelArgs& a, const PGeo& g, do
     } else {
         pu[0] = fu[0]; pu[1] = fu[1]; pv[0] = fv[0]; pv[1] = fv[1];
     }
-    if (M) {
-        unsigned char* pm = M + (size_t)y * a.mask_pitch + xb;
+    if (pm) {
         pm[0] = (unsigned char)(okbits & 1u);
         pm[1] = (unsigned char)((okbits >> 1) & 1u);
     }
     if (a.stats) {
-        unsigned rc = 0;
 #pragma unroll
         for (int q = 0; q < 2; ++q) {
             // val = sqrt(u^2 + v^2); !(val < mag_thresh)  <=>  !(u^2 + v^2 < mag2)
             const double s2 = dadd(dmul(fu[q], fu[q]), dmul(fv[q], fv[q]));
-            if (!(s2 < mag2)) { st.x += (unsigned)(xb + q); rc += 1u; }
+            if (!(s2 < mag2)) { sx += (unsigned)(xb + q); sc += 1u; }
         }
-        st.c += rc;
-        st.y += (unsigned long long)rc * (unsigned)y;
     }
 }
 
+// P4 of one output row y (block row i of the window sums): lane L < OUT_LANES owns the column pairs L
+// and L + OUT_LANES of the strip's 2 OUT_LANES pairs, so that the lanes' 16-byte accesses to u, v are
+// contiguous; pair p = (quad p / 2, half p % 2) of the pair-split sum rows.
 template <int R, bool VEC>
-__device__ __forceinline__ void phase_solve(const LevelArgs& a, const PGeo& g, double* __restrict__ U,
-                                            double* __restrict__ V, unsigned char* __restrict__ M, int m0,
-                                            int i_lo, int i_hi, const double* s_prod, StatAcc& st, int t_begin,
-                                            int t_end, int nthr)
+__device__ __forceinline__ void phase_solve_row(const LevelArgs& a, const PGeo& g, double* __restrict__ U,
+                                                double* __restrict__ V, unsigned char* __restrict__ M, int y,
+                                                const double* s_row, StatAcc& st)
 {
     using C = PhaseCfg<R>;
-    constexpr int NPAIR = C::OUT_COLS / 2;                   // task = (row, pair of columns)
-    const int W = g.W;
+    const int L = threadIdx.x & 31;
+    const int xb = g.xo0 + 2 * L;
+    if (L >= C::OUT_LANES || xb >= g.W) return;          // W even: a pair exists or it does not
     const double det_eps = a.det_eps, mag2 = a.mag2_thresh;
-    int ir = t_begin / NPAIR, pr = t_begin - ir * NPAIR;
-    for (int t = t_begin; t < t_end; t += nthr, pr += nthr) {
-        if (pr >= NPAIR) { pr -= NPAIR; ++ir; }              // nthr = 32 <= NPAIR
-        const int i = i_lo + ir;
-        const int xb = g.xo0 + 2 * pr;                       // even; W even: both columns exist or none
-        if (xb >= W) continue;
-        const double* sp = s_prod + 2 * (pr >> 1) + C::PHALF * (pr & 1) + i * (5 * C::PPITCH);
-        const int y = g.y0 + m0 + i;
-        const double2 sxx = lds2(sp), syy = lds2(sp + C::PPITCH), sxy = lds2(sp + 2 * C::PPITCH);
-        const double2 sxt = lds2(sp + 3 * C::PPITCH), syt = lds2(sp + 4 * C::PPITCH);
-        solve_pair<R, VEC>(a, g, U, V, M, y, xb, sxx, syy, sxy, sxt, syt, det_eps, mag2, st);
+    const bool yin = y >= R && y <= g.H - 1 - R;
+    const int off = y * (int)a.uv_pitch + xb;            // < 2^31 (checked by the launcher)
+    unsigned char* pm = M ? M + (size_t)y * a.mask_pitch + xb : nullptr;
+    const double* sp = s_row + (L & 1) * C::PHALF + 2 * (L >> 1);
+    unsigned sx = 0, sc = 0;
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        if (h == 1 && xb + 2 * C::OUT_LANES >= g.W) break;
+        const double* q = sp + h * C::OUT_LANES;
+        const int dx = 2 * C::OUT_LANES * h;
+        solve_pair<R, VEC>(a, g, U + off + dx, V + off + dx, pm ? pm + dx : nullptr, yin, xb + dx, lds2(q),
+                           lds2(q + C::PPITCH), lds2(q + 2 * C::PPITCH), lds2(q + 3 * C::PPITCH), lds2(q + 4 * C::PPITCH),
+                           det_eps, mag2, sx, sc);
     }
+    st.x += sx;
+    st.c += sc;
+    st.y += (unsigned long long)(sc * (unsigned)y);      // < 4 * 32767
 }
 
 // ------------------------------------------------------------------------------ R = 1: P2, P4
@@ -679,26 +811,75 @@ __device__ __forceinline__ void phase_solve1(const LevelArgs& a, const PGeo& g, 
     }
     const double det_eps = a.det_eps, mag2 = a.mag2_thresh;
     if (!active) return;
+    const bool yin = y >= 1 && y <= g.H - 2;
+    const int off = y * (int)a.uv_pitch + xb;            // < 2^31 (checked by the launcher)
+    unsigned char* pm = M ? M + (size_t)y * a.mask_pitch + xb : nullptr;
+    unsigned sx = 0, sc = 0;
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
         if (xb + 2 * h >= g.W) break;
-        solve_pair<1, VEC>(a, g, U, V, M, y, xb + 2 * h, make_double2(S[0][2 * h], S[0][2 * h + 1]),
-                      make_double2(S[1][2 * h], S[1][2 * h + 1]), make_double2(S[2][2 * h], S[2][2 * h + 1]),
-                      make_double2(S[3][2 * h], S[3][2 * h + 1]), make_double2(S[4][2 * h], S[4][2 * h + 1]), det_eps,
-                      mag2, st);
+        solve_pair<1, VEC>(a, g, U + off + 2 * h, V + off + 2 * h, pm ? pm + 2 * h : nullptr, yin, xb + 2 * h,
+                           make_double2(S[0][2 * h], S[0][2 * h + 1]), make_double2(S[1][2 * h], S[1][2 * h + 1]),
+                           make_double2(S[2][2 * h], S[2][2 * h + 1]), make_double2(S[3][2 * h], S[3][2 * h + 1]),
+                           make_double2(S[4][2 * h], S[4][2 * h + 1]), det_eps, mag2, sx, sc);
     }
+    st.x += sx;
+    st.c += sc;
+    st.y += (unsigned long long)(sc * (unsigned)y);
 }
 
 // ------------------------------------------------------------------------------ kernel
-template <int R, bool VEC>
-__global__ void __launch_bounds__(PH_NT, 1) lk_level_phase_kernel(LevelArgs a, int th)
+// Step geometry: step s warps fine rows vy0 + r - 1, r = r_lo .. WIN, and needs the coarse rows
+// ka .. ka + nk - 1.
+struct Step { int vy0, r_lo, sb, ka, nk; bool any; };
+
+template <int R>
+__device__ __forceinline__ Step step_geo(const PGeo& g, int n_steps, int s)
 {
     using C = PhaseCfg<R>;
-    extern __shared__ __align__(16) double sm[];
+    const int H = g.H;
+    Step q;
+    q.vy0 = g.y0 - R + s * C::WIN;                 // product row of block row 0
+    q.r_lo = s == 0 ? 0 : 1;
+    q.sb = (s * C::WIN) % C::AB_ROWS;
+    // rows [vlo, vhi]; source rows after border handling: [lo, hi]
+    const int vlo = q.vy0 + q.r_lo - 1, vhi = q.vy0 + C::WIN - 1;
+    int lo = max(vlo, 0), hi = min(vhi, H - 1);
+    if (vlo <= -1 && vhi >= -1) { lo = 0; hi = max(hi, min(1, H - 1)); }
+    q.ka = (lo >> 1) - 1;
+    q.nk = (hi >> 1) + 2 - q.ka;
+    q.any = lo <= hi && s < n_steps;
+    return q;
+}
+
+__device__ __forceinline__ void stats_flush(const LevelArgs& a, int pair, StatAcc st)
+{
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        st.x += __shfl_xor_sync(0xffffffffu, st.x, o);
+        st.y += __shfl_xor_sync(0xffffffffu, st.y, o);
+        st.c += __shfl_xor_sync(0xffffffffu, st.c, o);
+    }
+    if ((threadIdx.x & 31) == 0 && st.c != 0) {   // integer-valued sums: exact in any order
+        atomicAdd(&a.stats[pair].sum_x, (double)st.x);
+        atomicAdd(&a.stats[pair].sum_y, (double)st.y);
+        atomicAdd(&a.stats[pair].count, (double)st.c);
+    }
+}
+
+template <int R, bool VEC>
+__global__ void __launch_bounds__(PH_NT, 1) lk_level_phase_kernel(const __grid_constant__ CUtensorMap tmu,
+                                                                  const __grid_constant__ CUtensorMap tmv, LevelArgs a,
+                                                                  int th)
+{
+    using C = PhaseCfg<R>;
+    extern __shared__ __align__(128) double sm[];
     double* s_prod = sm;
-    double* s_ab = s_prod + C::PROD_D;
-    double* s_hr = s_ab + C::AB_D;
-    double* s_vs = s_hr + C::HR_D;
+    double* s_ab = sm + C::O_AB;
+    double* s_hr = sm + C::O_HR;
+    double* s_cr = sm + C::O_CR;
+    uint64_t* s_bar = reinterpret_cast<uint64_t*>(sm + C::O_BAR);
+    uint32_t* s_tmem = reinterpret_cast<uint32_t*>(sm + C::O_BAR + 1);
 
     PGeo g;
     g.W = a.w;
@@ -710,20 +891,17 @@ __global__ void __launch_bounds__(PH_NT, 1) lk_level_phase_kernel(LevelArgs a, i
     g.has_coarse = a.cu != nullptr;
     g.edge = g.c0 < 0 || g.c0 + PH_PC > a.w;
     const int pair = blockIdx.z;
-    const int H = g.H;
+    const int warp = threadIdx.x >> 5;
 
     const double* __restrict__ A = a.A + (size_t)pair * a.a_pair_stride;
     const double* __restrict__ B = a.B + (size_t)pair * a.b_pair_stride;
-    const double* __restrict__ cu = g.has_coarse ? a.cu + (size_t)pair * a.c_pair_stride : nullptr;
-    const double* __restrict__ cv = g.has_coarse ? a.cv + (size_t)pair * a.c_pair_stride : nullptr;
     double* U = a.u + (size_t)pair * a.uv_pair_stride;
     double* V = a.v + (size_t)pair * a.uv_pair_stride;
     unsigned char* M = a.mask ? a.mask + (size_t)pair * a.mask_pair_stride : nullptr;
-    g.vec_img = ((reinterpret_cast<uintptr_t>(A) | reinterpret_cast<uintptr_t>(B) | (a.img_pitch * 8)) & 15) == 0;
-    g.vec_uv = ((reinterpret_cast<uintptr_t>(U) | reinterpret_cast<uintptr_t>(V) | (a.uv_pitch * 8)) & 15) == 0;
-    g.vec_c = false;
 
     // P3 ownership: thread -> (channel, pair of output columns)
+    constexpr int V_WARPS = (5 * C::VPAIRS + 31) / 32;
+    static_assert((V_WARPS + 3) / 4 * C::TM_SLOT <= C::TM_COLS && 8 * R <= C::TM_SLOT, "tensor-memory slots");
     const bool v_task = threadIdx.x < 5 * C::VPAIRS;
     int voff;
     {
@@ -731,65 +909,74 @@ __global__ void __launch_bounds__(PH_NT, 1) lk_level_phase_kernel(LevelArgs a, i
         const int half = q / C::OUT_LANES, ol = q - half * C::OUT_LANES;
         voff = v_task ? ch * C::PPITCH + half * C::PHALF + 2 * ol : 0;
     }
-    for (int t = threadIdx.x; t < C::VS_D; t += PH_NT) s_vs[t] = 0.0;
+    if (threadIdx.x == 0) {
+        mbar_init(s_bar, 1);
+        mbar_fence_init();
+    }
+    if (warp == 0) tmem_alloc(s_tmem, C::TM_COLS);
+    tmem_fence_before_sync();
     __syncthreads();
+    tmem_fence_after_sync();
+    const uint32_t tm_base = *s_tmem;
+    const uint32_t tm_mine = tmem_addr(tm_base, (warp >> 2) * C::TM_SLOT);
+    if (warp < V_WARPS) {                                // no previous block yet: its raw rows are 0
+        const double z[4] = {0.0, 0.0, 0.0, 0.0};
+#pragma unroll
+        for (int c = 0; c < R; ++c) tmem_st4(tm_mine + 8 * c, z);
+        tmem_wait_st();
+    }
     StatAcc st = {0, 0, 0};
 
     const int rows = g.y1 - g.y0;
     const int n_steps = (rows + 2 * R + C::WIN - 1) / C::WIN;
-    const int warp = threadIdx.x >> 5;
-
-    // Step s warps fine rows vy0 + r - 1, r = r_lo .. WIN, and needs the coarse rows ka .. ka+nk-1.
-    struct Step { int vy0, r_lo, sb, ka, nk; bool any; };
-    auto step_geo = [&](int s) {
-        Step q;
-        q.vy0 = g.y0 - R + s * C::WIN;                 // product row of block row 0
-        q.r_lo = s == 0 ? 0 : 1;
-        q.sb = (s * C::WIN) % C::AB_ROWS;
-        // rows [vlo, vhi]; source rows after border handling: [lo, hi]
-        const int vlo = q.vy0 + q.r_lo - 1, vhi = q.vy0 + C::WIN - 1;
-        int lo = max(vlo, 0), hi = min(vhi, H - 1);
-        if (vlo <= -1 && vhi >= -1) { lo = 0; hi = max(hi, min(1, H - 1)); }
-        q.ka = (lo >> 1) - 1;
-        q.nk = (hi >> 1) + 2 - q.ka;
-        q.any = lo <= hi && s < n_steps;
-        return q;
-    };
 
     // Schedule of a step (two block-wide barriers):
-    //   beta : P2(s), with the loads of P0(s+1) in flight meanwhile
+    //   beta : thread 0 hands the coarse rows of step s+1 to the copy engine; P2(s); then the horizontal
+    //          pyrUp pass over the landed rows
     //   gamma: the first V_WARPS warps ("V") run P3(s) and signal barrier 1; every warp then warps
-    //          its row of P1(s+1); finally P4(s), for which the other warps ("O") wait on barrier 1.
+    //          its row of P1(s+1); finally P4(s) row by row in the warps that have time for it: the
+    //          other warps ("O"), which wait on barrier 1 first, and the V warps without a P1 row.
     //          The latency-bound gathers thus overlap the shared-memory-bound vertical sums and
     //          the arithmetic of the solve.
     // The loop starts at s = -1 (only P0(0), P1(0)) so that every phase has a single call site:
     // the code of a step has to stay small enough for the instruction cache.
-    constexpr int V_WARPS = (5 * C::VPAIRS + 31) / 32;
     constexpr int O_WARPS = PH_NW - V_WARPS;
     static_assert(C::WIN - O_WARPS < V_WARPS, "not enough warps for the rows of P1");
+    constexpr int N_VR = C::WIN - O_WARPS > 0 ? C::WIN - O_WARPS : 0;     // V warps with a P1 row
     // rows of P1: O warps take WIN, WIN-1, ...; V warps 1, 2, ...; the last V warp has no row in
     // steady state and takes row 0, which only exists in the first step
     const int my_row = warp >= V_WARPS ? C::WIN - (warp - V_WARPS)
                                        : (1 + warp <= C::WIN - O_WARPS ? 1 + warp : (warp == V_WARPS - 1 ? 0 : -1));
-    Step cur = step_geo(0);
+    // rows of P4: block row i goes to the warp that warps row i + 1 in P1 (one P1 row and one P4 row per
+    // warp and step); PH_P4_MODE 0: the O warps and the V warps without a P1 row share them round robin
+#ifndef PH_P4_MODE
+#define PH_P4_MODE 1
+#endif
+    constexpr int P4_N = PH_P4_MODE ? C::WIN : O_WARPS + (V_WARPS - N_VR);
+    const int p4_idx = PH_P4_MODE ? (my_row >= 1 ? my_row - 1 : -1)
+                                  : (warp >= V_WARPS ? warp - V_WARPS : (warp >= N_VR ? O_WARPS + warp - N_VR : -1));
+    Step cur = step_geo<R>(g, n_steps, 0);
     cur.any = false;
     int k_have = -1000;                                // highest coarse row in the ring
+    unsigned up_par = 0;                               // phase parity of the landing-buffer barrier
 #ifdef PH_PROF
     long long prof_acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     long long prof_t = clock64();
 #endif
     for (int s = -1; s < n_steps; ++s) {
-        const Step nxt = step_geo(s + 1);
+        const Step nxt = step_geo<R>(g, n_steps, s + 1);
         PH_MARK(7);
         {
             // coarse rows of the next step that are not in the ring yet (consecutive steps overlap)
-            UpPre q;
             const bool up = nxt.any && g.has_coarse;
-            const int k_from = max(nxt.ka, k_have + 1), n_new = nxt.ka + nxt.nk - k_from;
-            if (up) up_rows_issue<C::HR_ROWS>(a, g, cu, cv, k_from, n_new, q);
+            const int k_from = max(nxt.ka, k_have + 1), n_new = max(nxt.ka + nxt.nk - k_from, 0);
+            if (up && threadIdx.x == 0)
+                up_rows_issue(&tmu, &tmv, (g.c0 >> 1) - 2, a.hc, pair, k_from, n_new, s_cr, s_bar);
             if (s >= 0) phase_products<R>(g, cur.vy0, cur.sb, s_ab, s_prod);
             if (up) {
-                up_rows_finish(a, g, cu, cv, k_from, n_new, q, s_hr);
+                mbar_wait(s_bar, up_par);
+                up_par ^= 1u;
+                up_rows_hpass<PH_NT>(g, a.wc, k_from, n_new, s_cr, s_hr);
                 k_have = nxt.ka + nxt.nk - 1;
             }
         }
@@ -799,7 +986,9 @@ __global__ void __launch_bounds__(PH_NT, 1) lk_level_phase_kernel(LevelArgs a, i
         const int m0 = C::WIN * (s - 1) + 1;           // output row (relative to y0) of block row 0
         const int i_lo = max(0, -m0), i_hi = s >= 0 ? min(C::WIN, rows - m0) : 0;
         if (warp < V_WARPS && s >= 0) {
-            if (v_task) phase_vertical<R>(s_prod + voff, s_vs + voff);
+#ifndef PH_KNOCK_P3
+            phase_vertical<R>(s_prod + voff, tm_mine, v_task);
+#endif
             asm volatile("bar.arrive 1, %0;" ::"n"(PH_NT) : "memory");
             asm volatile("bar.sync 2, %0;" ::"n"(V_WARPS * 32) : "memory");   // P3 done in all V warps
         }
@@ -810,33 +999,15 @@ __global__ void __launch_bounds__(PH_NT, 1) lk_level_phase_kernel(LevelArgs a, i
         }
         PH_MARK(3);
         if (s >= 0) {
-            // P4 tasks (row, column pair), in chunks of 32, are split so that all warps finish
-            // together: a V warp with a P1 row takes x chunks, an O warp (no P3) about one more,
-            // the V warps without a P1 row the rest (about five more each).
-            const int n4 = (i_hi - i_lo) * (C::OUT_COLS / 2);
-            const int nch = (n4 + 31) >> 5;
-            constexpr int N_VR = C::WIN - O_WARPS > 0 ? C::WIN - O_WARPS : 0;     // V warps with a P1 row
-            constexpr int N_VI = V_WARPS - N_VR;
-            const int x16 = max(0, 16 * nch - PH_IDLE16 * N_VI - PH_O16 * O_WARPS) / PH_NW;   // x in 1/16 chunks
-            const int q_vr = (x16 + 8) >> 4, q_o = (x16 + PH_O16 + 8) >> 4;
-            int c0, c1;
-            if (warp >= V_WARPS) {
-                asm volatile("bar.sync 1, %0;" ::"n"(PH_NT) : "memory");
-                c0 = (warp - V_WARPS) * q_o;
-                c1 = c0 + q_o;
-            } else if (warp < N_VR) {
-                c0 = O_WARPS * q_o + warp * q_vr;
-                c1 = c0 + q_vr;
-            } else {
-                const int base = O_WARPS * q_o + N_VR * q_vr;
-                const int rest = max(0, nch - base), k = warp - N_VR;
-                c0 = base + (rest * k) / N_VI;
-                c1 = base + (rest * (k + 1)) / N_VI;
-            }
-            c0 = min(c0, nch);
-            c1 = min(c1, nch);
+            if (warp >= V_WARPS) asm volatile("bar.sync 1, %0;" ::"n"(PH_NT) : "memory");
             PH_MARK(4);
-            phase_solve<R, VEC>(a, g, U, V, M, m0, i_lo, i_hi, s_prod, st, 32 * c0 + (threadIdx.x & 31), min(32 * c1, n4), 32);
+#ifndef PH_KNOCK_P4
+            if (p4_idx >= 0)
+#else
+            if (p4_idx >= 1000)
+#endif
+                for (int i = i_lo + p4_idx; i < i_hi; i += P4_N)
+                    phase_solve_row<R, VEC>(a, g, U, V, M, g.y0 + m0 + i, s_prod + i * (5 * C::PPITCH), st);
         }
         PH_MARK(5);
         __syncthreads();
@@ -847,38 +1018,30 @@ __global__ void __launch_bounds__(PH_NT, 1) lk_level_phase_kernel(LevelArgs a, i
     if (blockIdx.x == 1 && blockIdx.y == 0 && blockIdx.z == 0 && (threadIdx.x & 31) == 0 && a.w >= 1920)
         for (int i = 0; i < 8; ++i) atomicAdd(&g_phase_prof[warp * 8 + i], (unsigned long long)prof_acc[i]);
 #endif
-
-    if (a.stats) {
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            st.x += __shfl_xor_sync(0xffffffffu, st.x, o);
-            st.y += __shfl_xor_sync(0xffffffffu, st.y, o);
-            st.c += __shfl_xor_sync(0xffffffffu, st.c, o);
-        }
-        if ((threadIdx.x & 31) == 0 && st.c != 0) {   // integer-valued sums: exact in any order
-            atomicAdd(&a.stats[pair].sum_x, (double)st.x);
-            atomicAdd(&a.stats[pair].sum_y, (double)st.y);
-            atomicAdd(&a.stats[pair].count, (double)st.c);
-        }
-    }
+    if (a.stats) stats_flush(a, pair, st);
+    if (warp == 0) tmem_dealloc(tm_base, C::TM_COLS);    // after the loop's last block-wide barrier
 }
 
 // ------------------------------------------------------------------------------ kernel, R = 1
 // Same strip march with WIN = 15 rows per step.  Schedule of a step (two block-wide barriers):
-//   beta : P2(s) raw products -> ring, with the loads of P0(s+1) in flight
+//   beta : coarse rows of step s+1 -> copy engine; P2(s) raw products -> ring; horizontal pyrUp pass
 //   gamma: every warp warps its row of P1(s+1) and solves its output row of P4(s); odd warps
 //          solve first, so that the latency-bound gathers of one half overlap the FP64 work
 //          of the other.
 // Output row n - 2 (relative to y0) is produced when product row n = s WIN + i has arrived.
 template <bool VEC>
-__global__ void __launch_bounds__(PhaseCfg<1>::NT, PhaseCfg<1>::CTAS) lk_level_phase1_kernel(LevelArgs a, int th)
+__global__ void __launch_bounds__(PhaseCfg<1>::NT, PhaseCfg<1>::CTAS)
+    lk_level_phase1_kernel(const __grid_constant__ CUtensorMap tmu, const __grid_constant__ CUtensorMap tmv, LevelArgs a,
+                           int th)
 {
     constexpr int R = 1;
     using C = PhaseCfg<1>;
-    extern __shared__ __align__(16) double sm[];
+    extern __shared__ __align__(128) double sm[];
     double* s_prod = sm;
-    double* s_ab = s_prod + C::PROD_D;
-    double* s_hr = s_ab + C::AB_D;
+    double* s_ab = sm + C::O_AB;
+    double* s_hr = sm + C::O_HR;
+    double* s_cr = sm + C::O_CR;
+    uint64_t* s_bar = reinterpret_cast<uint64_t*>(sm + C::O_BAR);
 
     PGeo g;
     g.W = a.w;
@@ -890,54 +1053,42 @@ __global__ void __launch_bounds__(PhaseCfg<1>::NT, PhaseCfg<1>::CTAS) lk_level_p
     g.has_coarse = a.cu != nullptr;
     g.edge = g.c0 < 0 || g.c0 + PH_PC > a.w;
     const int pair = blockIdx.z;
-    const int H = g.H;
 
     const double* __restrict__ A = a.A + (size_t)pair * a.a_pair_stride;
     const double* __restrict__ B = a.B + (size_t)pair * a.b_pair_stride;
-    const double* __restrict__ cu = g.has_coarse ? a.cu + (size_t)pair * a.c_pair_stride : nullptr;
-    const double* __restrict__ cv = g.has_coarse ? a.cv + (size_t)pair * a.c_pair_stride : nullptr;
     double* U = a.u + (size_t)pair * a.uv_pair_stride;
     double* V = a.v + (size_t)pair * a.uv_pair_stride;
     unsigned char* M = a.mask ? a.mask + (size_t)pair * a.mask_pair_stride : nullptr;
-    g.vec_img = ((reinterpret_cast<uintptr_t>(A) | reinterpret_cast<uintptr_t>(B) | (a.img_pitch * 8)) & 15) == 0;
-    g.vec_uv = ((reinterpret_cast<uintptr_t>(U) | reinterpret_cast<uintptr_t>(V) | (a.uv_pitch * 8)) & 15) == 0;
-    g.vec_c = false;
     StatAcc st = {0, 0, 0};
+    if (threadIdx.x == 0) {
+        mbar_init(s_bar, 1);
+        mbar_fence_init();
+    }
+    __syncthreads();
 
     const int rows = g.y1 - g.y0;
     const int n_steps = (rows + 2 * R + C::WIN - 1) / C::WIN;
     const int warp = threadIdx.x >> 5;
 
-    struct Step { int vy0, r_lo, sb, ka, nk; bool any; };
-    auto step_geo = [&](int s) {
-        Step q;
-        q.vy0 = g.y0 - R + s * C::WIN;                 // product row of block row 0
-        q.r_lo = s == 0 ? 0 : 1;
-        q.sb = (s * C::WIN) % C::AB_ROWS;
-        const int vlo = q.vy0 + q.r_lo - 1, vhi = q.vy0 + C::WIN - 1;
-        int lo = max(vlo, 0), hi = min(vhi, H - 1);
-        if (vlo <= -1 && vhi >= -1) { lo = 0; hi = max(hi, min(1, H - 1)); }
-        q.ka = (lo >> 1) - 1;
-        q.nk = (hi >> 1) + 2 - q.ka;
-        q.any = lo <= hi && s < n_steps;
-        return q;
-    };
     // rows of P1: warp w takes row w + 1; the last warp takes row 0, which only exists in the first step
     const int my_row = warp < C::WIN ? warp + 1 : 0;
-    Step cur = step_geo(0);
+    Step cur = step_geo<1>(g, n_steps, 0);
     cur.any = false;
     int k_have = -1000;
+    unsigned up_par = 0;
     for (int s = -1; s < n_steps; ++s) {
-        const Step nxt = step_geo(s + 1);
+        const Step nxt = step_geo<1>(g, n_steps, s + 1);
         const int n0 = s >= 0 ? (s * C::WIN) % C::PR_ROWS : 0;
         {
-            UpPreT<C::UPK> q;
             const bool up = nxt.any && g.has_coarse;
-            const int k_from = max(nxt.ka, k_have + 1), n_new = nxt.ka + nxt.nk - k_from;
-            if (up) up_rows_issue<C::HR_ROWS, C::NT, C::UPK>(a, g, cu, cv, k_from, n_new, q);
+            const int k_from = max(nxt.ka, k_have + 1), n_new = max(nxt.ka + nxt.nk - k_from, 0);
+            if (up && threadIdx.x == 0)
+                up_rows_issue(&tmu, &tmv, (g.c0 >> 1) - 2, a.hc, pair, k_from, n_new, s_cr, s_bar);
             if (s >= 0) phase_products1(g, cur.vy0, cur.sb, n0, s_ab, s_prod);
             if (up) {
-                up_rows_finish<C::NT, C::UPK>(a, g, cu, cv, k_from, n_new, q, s_hr);
+                mbar_wait(s_bar, up_par);
+                up_par ^= 1u;
+                up_rows_hpass<C::NT>(g, a.wc, k_from, n_new, s_cr, s_hr);
                 k_have = nxt.ka + nxt.nk - 1;
             }
         }
@@ -963,20 +1114,7 @@ __global__ void __launch_bounds__(PhaseCfg<1>::NT, PhaseCfg<1>::CTAS) lk_level_p
         __syncthreads();
         cur = nxt;
     }
-
-    if (a.stats) {
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            st.x += __shfl_xor_sync(0xffffffffu, st.x, o);
-            st.y += __shfl_xor_sync(0xffffffffu, st.y, o);
-            st.c += __shfl_xor_sync(0xffffffffu, st.c, o);
-        }
-        if ((threadIdx.x & 31) == 0 && st.c != 0) {
-            atomicAdd(&a.stats[pair].sum_x, (double)st.x);
-            atomicAdd(&a.stats[pair].sum_y, (double)st.y);
-            atomicAdd(&a.stats[pair].count, (double)st.c);
-        }
-    }
+    if (a.stats) stats_flush(a, pair, st);
 }
 
 template <int R, bool VEC>
@@ -990,13 +1128,21 @@ cudaError_t launch_phase_v(const LevelArgs& a, int n_pairs, cudaStream_t s, unsi
         else e = opt_in.ensure((const void*)lk_level_phase_kernel<R, VEC>, C::SMEM_BYTES);
         if (e != cudaSuccess) return e;
     }
+    // tensor maps of the coarse flow planes (x, y, pair), one box = CR_W columns of one row
+    CUtensorMap tmu, tmv;
+    memset(&tmu, 0, sizeof tmu);
+    memset(&tmv, 0, sizeof tmv);
+    if (a.cu) {
+        cudaError_t e = tma_map_planes_f64(&tmu, a.cu, a.wc, a.hc, a.c_pitch, a.c_pair_stride, n_pairs, CR_W, 1);
+        if (e == cudaSuccess) e = tma_map_planes_f64(&tmv, a.cv, a.wc, a.hc, a.c_pitch, a.c_pair_stride, n_pairs, CR_W, 1);
+        if (e != cudaSuccess) return e;
+    }
     const int strips = (a.w + C::OUT_COLS - 1) / C::OUT_COLS;
     // Chunk height: a multiple of the vertical block length, so that block boundaries sit at
     // the same absolute rows whatever the chunking (bit-identical results for any batch size).
     // Pick the height that minimises (waves of resident CTAs) x (steps a CTA runs).
     long resident = current_sm_count();
-    int nt = PH_NT;
-    if constexpr (R == 1) { resident *= C::CTAS; nt = C::NT; }
+    if constexpr (R == 1) resident *= C::CTAS;
     const int max_m = (a.h + C::WIN - 1) / C::WIN;
     long best_cost = -1;
     int th = C::WIN * max_m;
@@ -1011,8 +1157,8 @@ cudaError_t launch_phase_v(const LevelArgs& a, int n_pairs, cudaStream_t s, unsi
     }
     const int chunks = (a.h + th - 1) / th;
     dim3 grid(strips, chunks, n_pairs);
-    if constexpr (R == 1) lk_level_phase1_kernel<VEC><<<grid, nt, C::SMEM_BYTES, s>>>(a, th);
-    else lk_level_phase_kernel<R, VEC><<<grid, nt, C::SMEM_BYTES, s>>>(a, th);
+    if constexpr (R == 1) lk_level_phase1_kernel<VEC><<<grid, C::NT, C::SMEM_BYTES, s>>>(tmu, tmv, a, th);
+    else lk_level_phase_kernel<R, VEC><<<grid, C::NT, C::SMEM_BYTES, s>>>(tmu, tmv, a, th);
     if (launches) *launches += 1;
     return cudaGetLastError();
 }
@@ -1030,7 +1176,9 @@ cudaError_t launch_phase(const LevelArgs& a, int n_pairs, cudaStream_t s, unsign
 }  // namespace
 
 // Handles R = 1..7 on even-width levels (statistics-only calls come with scratch flow planes from the
-// caller, of_api.cu); tiny / odd-sized levels and larger radii go to the other kernels.
+// caller, of_api.cu); tiny / odd-sized levels and larger radii go to the tile kernel.  The coarse flow
+// planes are read through tensor maps: 16-byte aligned base, even pitch / pair stride (the library's
+// own scratch planes always are).
 cudaError_t launch_lk_level_phase(const LevelArgs& a, int n_pairs, cudaStream_t s,
                                   unsigned long long* launches, bool* handled)
 {
@@ -1038,6 +1186,9 @@ cudaError_t launch_lk_level_phase(const LevelArgs& a, int n_pairs, cudaStream_t 
     if (!a.u || !a.v) return cudaSuccess;
     if (a.w < 4 || a.h < 2 || (a.w & 1)) return cudaSuccess;
     if (a.cu && (a.wc < 2 || a.w != 2 * a.wc || a.h != 2 * a.hc)) return cudaSuccess;
+    if (a.cu && (((reinterpret_cast<uintptr_t>(a.cu) | reinterpret_cast<uintptr_t>(a.cv)) & 15) || (a.c_pitch & 1) ||
+                 (a.c_pair_stride & 1) || !tma_encoder()))
+        return cudaSuccess;
     if ((unsigned long long)a.img_pitch * (unsigned long long)a.h >= (1ull << 31)) return cudaSuccess;
     if ((unsigned long long)a.uv_pitch * (unsigned long long)a.h >= (1ull << 31)) return cudaSuccess;
     *handled = true;
@@ -1058,6 +1209,17 @@ cudaError_t launch_lk_level_phase(const LevelArgs& a, int n_pairs, cudaStream_t 
 }  // namespace ofb
 
 #ifdef PH_PROF
+#ifdef PH_PROF1
+extern "C" __attribute__((visibility("default"))) int of_b200_debug_p1_prof(unsigned long long* out, int reset)
+{
+    cudaError_t e = cudaMemcpyFromSymbol(out, ofb::g_p1_prof, sizeof(unsigned long long) * 32 * 8);
+    if (e == cudaSuccess && reset) {
+        static unsigned long long z[32 * 8];
+        e = cudaMemcpyToSymbol(ofb::g_p1_prof, z, sizeof(z));
+    }
+    return (int)e;
+}
+#endif
 extern "C" __attribute__((visibility("default"))) int of_b200_debug_phase_prof(unsigned long long* out, int reset)
 {
     cudaError_t e = cudaMemcpyFromSymbol(out, ofb::g_phase_prof, sizeof(unsigned long long) * 32 * 8);

@@ -26,3 +26,13 @@ for wp in range(32):
     v = [buf[wp * 8 + i] / steps for i in range(8)]
     if sum(v) == 0: continue
     print("%4d " % wp + " ".join("%8.0f" % x for x in v) + " %8.0f" % sum(v))
+if hasattr(lib, "of_b200_debug_p1_prof"):
+    # the counters were reset with the others only if reset was called on them too: report totals / all calls
+    lib.of_b200_debug_p1_prof(buf, 0)
+    names = ["setup", "vert", "park", "tapsA", "blendA", "tapsB", "blendB", "store"]
+    print("P1 breakdown (cycles per step, includes the warm-up calls: scaled by %d/%d)" % (reps, reps + 3))
+    print("warp " + " ".join("%8s" % x for x in names) + "    total")
+    for wp in range(32):
+        v = [buf[wp * 8 + i] / (74 * (reps + 3)) for i in range(8)]
+        if sum(v) == 0: continue
+        print("%4d " % wp + " ".join("%8.0f" % x for x in v) + " %8.0f" % sum(v))
