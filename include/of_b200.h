@@ -225,6 +225,32 @@ enum { OF_LEVEL_FRAME1 = 0, OF_LEVEL_FRAME2 = 1, OF_LEVEL_FLOW_U = 2, OF_LEVEL_F
 OF_API of_status of_ctx_get_level_f64(of_ctx *ctx, int what, int level, int pair, double *dst,
                                       size_t dst_step_bytes, int *width, int *height);
 
+/* ---- single-process multi-GPU (frame pairs shard across the GPUs of one box) ---------
+ * The reference is one C++ process; this is the C/C++ way to put its frame stream on several GPUs:
+ * one context per device, one host thread per device inside each call, the n_frames - 1 consecutive
+ * pairs split into contiguous blocks (of_mgpu_partition), flow fields and statistics written straight
+ * into the caller's arrays.  A frame is never split and the devices exchange nothing (no collective).
+ * devices = NULL / n_devices = 0: every visible device.  Arguments as of_ctf_f64_stream /
+ * of_ctf_u8_stream (host pointers; pinned memory makes the copies asynchronous). */
+typedef struct of_mgpu of_mgpu;
+OF_API of_status of_mgpu_create(const int *devices, int n_devices, const of_params *params, of_mgpu **out);
+OF_API void of_mgpu_destroy(of_mgpu *m);
+OF_API int of_mgpu_device_count(const of_mgpu *m);
+OF_API of_ctx *of_mgpu_context(of_mgpu *m, int index);   /* the context of the index-th device (set_params, timing) */
+OF_API const char *of_mgpu_last_error_string(const of_mgpu *m); /* m may be NULL: last create error */
+/* Pairs [*first, *last) go to the index-th of n_devices devices. */
+OF_API of_status of_mgpu_partition(int n_pairs, int n_devices, int index, int *first, int *last);
+OF_API of_status of_mgpu_ctf_f64_stream(of_mgpu *m, const double *frames, int n_frames,
+                                 size_t frame_stride_bytes, int width, int height,
+                                 size_t step_bytes, int n_levels,
+                                 double *u, double *v, size_t uv_pair_stride_bytes,
+                                 size_t uv_step_bytes, of_gesture_stats *stats);
+OF_API of_status of_mgpu_ctf_u8_stream(of_mgpu *m, const unsigned char *frames, int n_frames,
+                                size_t frame_stride_bytes, int width, int height,
+                                size_t step_bytes, double alpha, double beta, int n_levels,
+                                double *u, double *v, size_t uv_pair_stride_bytes,
+                                size_t uv_step_bytes, of_gesture_stats *stats);
+
 /* Number of kernel launches issued through this context since creation (bench evidence). */
 OF_API unsigned long long of_ctx_launch_count(const of_ctx *ctx);
 

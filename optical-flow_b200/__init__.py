@@ -31,6 +31,8 @@ EXPORTS = (
     "of_ctx_synchronize", "of_ctx_launch_count", "of_ctx_set_timing", "of_ctx_get_timing",
     "of_bgr2gray_u8_dev", "of_live_diff_f64_dev", "of_live_diff_f64", "of_ctf_u8_stream",
     "of_ctx_get_level_f64",
+    "of_mgpu_create", "of_mgpu_destroy", "of_mgpu_device_count", "of_mgpu_context", "of_mgpu_last_error_string",
+    "of_mgpu_partition", "of_mgpu_ctf_f64_stream", "of_mgpu_ctf_u8_stream",
 )
 
 
@@ -99,6 +101,17 @@ def lib():
     L.of_bgr2gray_u8_dev.argtypes = [vp, vp, ci, ci, sz, vp, sz, ci, vp]
     L.of_live_diff_f64_dev.argtypes = [vp, vp, vp, ci, ci, sz, dbl, ci, ci, vp, sz, vp]
     L.of_live_diff_f64.argtypes = [vp, vp, vp, ci, ci, ci, sz, ci, dbl, ci, ci, vp, sz]
+    L.of_mgpu_create.argtypes = [C.POINTER(ci), ci, C.POINTER(OfParams), C.POINTER(vp)]
+    L.of_mgpu_destroy.argtypes = [vp]
+    L.of_mgpu_destroy.restype = None
+    L.of_mgpu_device_count.argtypes = [vp]
+    L.of_mgpu_context.argtypes = [vp, ci]
+    L.of_mgpu_context.restype = vp
+    L.of_mgpu_last_error_string.argtypes = [vp]
+    L.of_mgpu_last_error_string.restype = C.c_char_p
+    L.of_mgpu_partition.argtypes = [ci, ci, ci, C.POINTER(ci), C.POINTER(ci)]
+    L.of_mgpu_ctf_f64_stream.argtypes = [vp, vp, ci, sz, ci, ci, sz, ci, vp, vp, sz, sz, vp]
+    L.of_mgpu_ctf_u8_stream.argtypes = [vp, vp, ci, sz, ci, ci, sz, dbl, dbl, ci, vp, vp, sz, sz, vp]
     L.of_ctx_synchronize.argtypes = [vp]
     L.of_ctx_launch_count.argtypes = [vp]
     L.of_ctx_launch_count.restype = C.c_ulonglong
@@ -405,3 +418,78 @@ class Context:
         self._check(lib().of_live_diff_f64_dev(self._h, cur_gray.data_ptr(), prev_gray.data_ptr(), w, h,
                                                cur_gray.stride(0), learning_rate, diff_thresh,
                                                morph_iterations, out.data_ptr(), out.stride(0) * 8, s))
+
+
+class MultiGpu:
+    """``of_mgpu``: the frame stream of the live loop sharded across several GPUs from ONE process (one
+    context and one host thread per device inside the C library; contiguous blocks of pairs)."""
+
+    def __init__(self, devices=None, win_radius: int = 1, det_eps: float = 0.0, mag_thresh: float = 20.0,
+                 count_thresh: int = 500):
+        L = lib()
+        p = default_params()
+        p.win_radius, p.det_eps = int(win_radius), float(det_eps)
+        p.mag_thresh, p.count_thresh = float(mag_thresh), int(count_thresh)
+        self._h = C.c_void_p()
+        if devices is None:
+            st = L.of_mgpu_create(None, 0, C.byref(p), C.byref(self._h))
+        else:
+            arr = (C.c_int * len(devices))(*[int(d) for d in devices])
+            st = L.of_mgpu_create(arr, len(devices), C.byref(p), C.byref(self._h))
+        if st != OF_OK:
+            raise OfError(st, (L.of_mgpu_last_error_string(None) or b"").decode())
+
+    @property
+    def device_count(self) -> int:
+        return int(lib().of_mgpu_device_count(self._h))
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h.value:
+            lib().of_mgpu_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @staticmethod
+    def partition(n_pairs: int, n_devices: int, index: int):
+        a, b = C.c_int(0), C.c_int(0)
+        st = lib().of_mgpu_partition(int(n_pairs), int(n_devices), int(index), C.byref(a), C.byref(b))
+        if st != OF_OK:
+            raise BadArgError(st, "bad partition arguments")
+        return a.value, b.value
+
+    def flow_stream(self, frames, nLevels: int, want_flow: bool = True, want_stats: bool = True, out_u=None,
+                    out_v=None, alpha: float = 1.0 / 255, beta: float = 0.0):
+        """Same contract as ``Context.flow_stream`` with the pairs split across the devices."""
+        f = np.asarray(frames)
+        if f.dtype not in (np.float64, np.uint8) or f.ndim != 3 or not f.flags.c_contiguous:
+            raise BadArgError(OF_E_BADARG, "frames must be a C-contiguous (n, H, W) float64 or uint8 array")
+        n, h, w = f.shape
+        u = v = None
+        if want_flow:
+            u = out_u if out_u is not None else np.empty((n - 1, h, w), np.float64)
+            v = out_v if out_v is not None else np.empty((n - 1, h, w), np.float64)
+        stats = np.zeros(n - 1, STATS_DTYPE) if want_stats else None
+        up = u.ctypes.data if want_flow else None
+        vp_ = v.ctypes.data if want_flow else None
+        sp = stats.ctypes.data if want_stats else None
+        if f.dtype == np.uint8:
+            st = lib().of_mgpu_ctf_u8_stream(self._h, f.ctypes.data, n, h * w, w, h, w, float(alpha), float(beta),
+                                             int(nLevels), up, vp_, h * w * 8, w * 8, sp)
+        else:
+            st = lib().of_mgpu_ctf_f64_stream(self._h, f.ctypes.data, n, h * w * 8, w, h, w * 8, int(nLevels), up, vp_,
+                                              h * w * 8, w * 8, sp)
+        if st != OF_OK:
+            msg = (lib().of_mgpu_last_error_string(self._h) or b"").decode()
+            raise (NotDivisibleError if st == OF_E_NOT_DIVISIBLE else BadArgError if st == OF_E_BADARG else OfError)(st, msg)
+        return u, v, stats

@@ -74,7 +74,7 @@ def build_library(force: bool = False, verbose: bool = False, defines=(), out: s
         if p.returncode:
             raise RuntimeError("nvcc failed on %s" % src)
     cmd = [nvcc, "-shared", "-cudart", "static", "-gencode", "arch=compute_100a,code=sm_100a",
-           "-o", LIB] + objs + ["-ldl"]
+           "-o", LIB] + objs + ["-ldl", "-lpthread"]
     subprocess.check_call(cmd)
     return LIB
 

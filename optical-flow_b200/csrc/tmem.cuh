@@ -32,23 +32,36 @@ __device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.
 // Address of column `col` for the calling warp: lane field = first lane of the warp's quarter.
 __device__ __forceinline__ uint32_t tmem_addr(uint32_t base, int col) { return base + (((threadIdx.x >> 5) & 3u) << 21) + (uint32_t)col; }
 
-// 4 doubles (8 columns) per thread
+// 4 doubles (8 columns) per thread.  The 64-bit values are split / joined inside the asm block so that
+// ptxas can keep them in the register pairs they already live in (no per-word moves).
 __device__ __forceinline__ void tmem_st4(uint32_t addr, const double (&v)[4])
 {
-    asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"r"(addr),
-                 "r"(__double2loint(v[0])), "r"(__double2hiint(v[0])), "r"(__double2loint(v[1])), "r"(__double2hiint(v[1])),
-                 "r"(__double2loint(v[2])), "r"(__double2hiint(v[2])), "r"(__double2loint(v[3])), "r"(__double2hiint(v[3]))
-                 : "memory");
+    asm volatile(
+        "{\n"
+        ".reg .b32 a<8>;\n"
+        "mov.b64 {a0, a1}, %1;\n"
+        "mov.b64 {a2, a3}, %2;\n"
+        "mov.b64 {a4, a5}, %3;\n"
+        "mov.b64 {a6, a7}, %4;\n"
+        "tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {a0, a1, a2, a3, a4, a5, a6, a7};\n"
+        "}\n" ::"r"(addr),
+        "d"(v[0]), "d"(v[1]), "d"(v[2]), "d"(v[3])
+        : "memory");
 }
 __device__ __forceinline__ void tmem_ld4(uint32_t addr, double (&v)[4])
 {
-    uint32_t r[8];
-    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
-                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
-                 : "r"(addr)
-                 : "memory");
-#pragma unroll
-    for (int k = 0; k < 4; ++k) v[k] = __hiloint2double((int)r[2 * k + 1], (int)r[2 * k]);
+    asm volatile(
+        "{\n"
+        ".reg .b32 a<8>;\n"
+        "tcgen05.ld.sync.aligned.32x32b.x8.b32 {a0, a1, a2, a3, a4, a5, a6, a7}, [%4];\n"
+        "mov.b64 %0, {a0, a1};\n"
+        "mov.b64 %1, {a2, a3};\n"
+        "mov.b64 %2, {a4, a5};\n"
+        "mov.b64 %3, {a6, a7};\n"
+        "}\n"
+        : "=d"(v[0]), "=d"(v[1]), "=d"(v[2]), "=d"(v[3])
+        : "r"(addr)
+        : "memory");
 }
 
 }  // namespace ofb
