@@ -6,7 +6,11 @@ Bars (BASELINE.json north_star / SURVEY.md 8(c)):
     flow is required BIT-EXACT against the FP64 oracle and <= 1e-6 against the %lf goldens
     (the reference harness's own tolerance, ParallelBasicPyr.cpp:787,818);
   * r > 1 (no reference summation order exists): validity mask identical, flow within
-    FLOW_TOL = 1e-3 px max-abs on valid pixels.
+    FLOW_TOL = 1e-3 px max-abs on valid pixels (north_star's wording).  A pixel that is not valid
+    (det == 0) carries only the upsampled flow of the coarser level; if a coarser pixel is
+    ill-conditioned beyond FP64 (relative determinant 6e-13 in the 1080p gesture stream) its
+    summation-order noise is handed down uncorrected, so those pixels get the looser bound
+    INVALID_TOL -- observed 2e-3 there against 8e-8 on the valid pixels of the same pair.
 """
 import os
 
@@ -18,6 +22,7 @@ from conftest import GOLDEN, load_gray_png
 pytestmark = pytest.mark.gpu
 
 FLOW_TOL = 1e-3   # px, north_star: "flow (u,v) must agree to <= 1e-3 px max-abs on valid pixels"
+INVALID_TOL = 1e-2   # px, r > 1 only: pixels outside the validity mask (upsampled coarse flow, see above)
 
 
 @pytest.fixture(scope="module")
@@ -35,8 +40,11 @@ def check(got, want, r, what=""):
         assert np.array_equal(u, uo) and np.array_equal(v, vo), \
             "%s: r=1 must be bit-exact; max|d| = %g" % (what, max(np.abs(u - uo).max(), np.abs(v - vo).max()))
     else:
-        err = max(np.abs(u - uo).max(), np.abs(v - vo).max())
-        assert err <= FLOW_TOL, "%s: max|dflow| = %g px" % (what, err)
+        e = np.maximum(np.abs(u - uo), np.abs(v - vo))
+        err = e[mo].max() if mo.any() else 0.0
+        assert err <= FLOW_TOL, "%s: max|dflow| = %g px on valid pixels" % (what, err)
+        err = e[~mo].max() if (~mo).any() else 0.0
+        assert err <= INVALID_TOL, "%s: max|dflow| = %g px outside the validity mask" % (what, err)
 
 
 # ------------------------------------------------------------------ known-answer tests
