@@ -3,6 +3,7 @@
 
     python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path
     python bench.py --impl reference --gpus N --steps K ...  # CPU baseline arm
+    python bench.py --config 4k ...                          # BASELINE.json configs[4] (3840x2160, L = 4)
 
 Workload (BASELINE.json configs[3], the configuration the metric is quoted on): synthetic
 1920x1080 grayscale video, 3-level pyramid, 15x15 window (r = 7), FP64.  One "step" = one batch
@@ -34,10 +35,23 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-W, H, LEVELS, RADIUS = 1920, 1080, 3, 7
+# BASELINE.json configs[3] (the configuration the metric is quoted on) and configs[4]
+CONFIGS = {
+    "1080p": {"w": 1920, "h": 1080, "levels": 3, "radius": 7, "pairs": 16, "ref_pairs": 2,
+              "metric": "frame_pairs_per_sec_1080p_3level_lk",
+              "workload": "synthetic 1920x1080 grayscale video, 3-level pyramid, 15x15 window (r=7), consecutive frame pairs"},
+    "4k": {"w": 3840, "h": 2160, "levels": 4, "radius": 7, "pairs": 8, "ref_pairs": 1,
+           "metric": "frame_pairs_per_sec_4k_4level_lk",
+           "workload": "synthetic 3840x2160 grayscale video, 4-level pyramid, 15x15 window (r=7), consecutive frame pairs"},
+}
+W, H, LEVELS, RADIUS = 1920, 1080, 3, 7      # set from --config in main()
 PAIRS = 16                      # frame pairs per step per GPU
-METRIC = "frame_pairs_per_sec_1080p_3level_lk"
+METRIC = CONFIGS["1080p"]["metric"]
+WORKLOAD = CONFIGS["1080p"]["workload"]
+REF_PAIRS = 2
 UNIT = "pairs/s"
+MIN_TIMED_S = 0.5               # the timed region repeats the K-step loop until this much has elapsed ...
+MIN_REPS = 5                    # ... and at least this many times; the median repetition is reported
 
 
 def level_sizes(w, h, L):
@@ -65,6 +79,29 @@ def measured_peaks():
         except Exception:
             pass
     return 6650.0, "fallback"
+
+
+def recorded(name):
+    """A committed measurement under profiles/ (ncu-derived constants the live run cannot take itself)."""
+    try:
+        return json.load(open(os.path.join(ROOT, "profiles", name)))
+    except Exception:
+        return None
+
+
+def fp64_roofline(radius, n_px, launch_ms, sm_mhz, n_sm):
+    """Second roofline of the level-0 kernel: FP64 issue.  ops_per_px = FP64 instructions (DADD + DMUL +
+    DFMA, per thread) the kernel executes per level-0 output pixel, counted by ncu on this kernel
+    (profiles/fp64_ops.json); peak = 64 FP64 lanes / clk / SM (tools/ubench.cu, profiles/r01_ubench.txt:
+    18.36 T instructions/s at 1.94 GHz on 148 SMs) at the SM clock sampled during the run."""
+    rec = recorded("fp64_ops.json")
+    if not rec or ("r%d" % radius) not in rec or not launch_ms or not sm_mhz:
+        return None
+    ops = float(rec["r%d" % radius])
+    achieved = ops * n_px / (launch_ms * 1e-3) / 1e12
+    peak = 64.0 * n_sm * sm_mhz * 1e6 / 1e12
+    return {"ops_per_px": ops, "achieved": achieved, "peak": peak, "unit": "T FP64 instructions/s",
+            "frac": achieved / peak, "source": rec.get("source")}
 
 
 class ClockSampler:
@@ -154,7 +191,7 @@ def synth(n_frames, seed=1234):
     return importlib.import_module("optical_flow_b200.synth").synth_frames(n_frames, H, W, seed=seed)
 
 
-def cpu_baseline_run(frames, n_pairs, repeats=1):
+def cpu_baseline_run(frames, n_pairs, repeats=1, radius=None):
     """Times the C+OpenMP oracle port (oracle/lk_oracle.c) on n_pairs pairs of the workload,
     all host threads.  Returns (pairs_per_s, cores, seconds)."""
     from oracle import c_oracle as CO
@@ -165,7 +202,8 @@ def cpu_baseline_run(frames, n_pairs, repeats=1):
     done = 0
     for _ in range(repeats):
         for k in range(n_pairs):
-            CO.coarse_to_fine(frames[k % (len(frames) - 1)], frames[k % (len(frames) - 1) + 1], LEVELS, RADIUS)
+            CO.coarse_to_fine(frames[k % (len(frames) - 1)], frames[k % (len(frames) - 1) + 1], LEVELS,
+                              RADIUS if radius is None else radius)
             done += 1
     dt = time.perf_counter() - t0
     return done / dt, cores, dt
@@ -175,21 +213,22 @@ def run_reference(args):
     """--impl reference: the reference's CPU implementation of the path.  The reference itself
     (OpenCV 2.4 C++) cannot be compiled in this image, so this times the oracle port of it
     (oracle/lk_oracle.c, C + OpenMP, every host thread) on the same workload; one step = a
-    bounded sample of SAMPLE pairs."""
+    bounded sample of REF_PAIRS pairs."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    sample = 2
+    sample = REF_PAIRS
     frames = synth(sample + 1)
     from oracle import c_oracle as CO
     CO.build()
     cores = CO.set_threads(host_threads())      # torchrun exports OMP_NUM_THREADS=1: use every host thread anyway
+    radius = args.radius
     for _ in range(max(args.warmup, 1)):
-        CO.coarse_to_fine(frames[0], frames[1], LEVELS, RADIUS)
+        CO.coarse_to_fine(frames[0], frames[1], LEVELS, radius)
     t0 = time.perf_counter()
     for _ in range(args.steps):
         for k in range(sample):
-            CO.coarse_to_fine(frames[k], frames[k + 1], LEVELS, RADIUS)
+            CO.coarse_to_fine(frames[k], frames[k + 1], LEVELS, radius)
     dt = time.perf_counter() - t0
     val = args.steps * sample / dt
     line = {
@@ -197,10 +236,10 @@ def run_reference(args):
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
         "data": "synthetic",
-        "config": {"workload": "synthetic 1920x1080 video, 3-level pyramid, 15x15 window (r=7), %d pairs per step" % sample,
-                   "width": W, "height": H, "levels": LEVELS, "win_radius": RADIUS},
+        "config": {"workload": WORKLOAD, "width": W, "height": H, "levels": LEVELS, "win_radius": radius,
+                   "pairs_per_step": sample},
         "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port",
-                         "sample": "%d steps x %d consecutive pairs of the synthetic 1080p stream, "
+                         "sample": "%d steps x %d consecutive pairs of the same synthetic stream, "
                                    "oracle/lk_oracle.c (gcc -O3 -fopenmp), all host threads" % (args.steps, sample)},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -251,24 +290,43 @@ def run_ours(args):
     barrier()
 
     # ---- device-resident timed region ------------------------------------------------------
+    # One repetition = args.steps steps between two CUDA events; repetitions go on until MIN_TIMED_S
+    # have elapsed (and at least MIN_REPS times), so that a short --steps still gives the clocks
+    # sampler and the per-launch statistics a real window.  The median repetition is reported.
     ctx.set_timing(True)
     lvl0_ms, lvl_ms, pyr_ms = [], [], []
     sampler = ClockSampler(torch.cuda.current_device() if os.environ.get("CUDA_VISIBLE_DEVICES") is None else local_rank)
     launches0 = ctx.launch_count
-    e0 = torch.cuda.Event(enable_timing=True)
-    e1 = torch.cuda.Event(enable_timing=True)
     sampler.start()
     barrier()
     sampler.mark()
-    e0.record()
-    for i in range(args.steps):
-        step()
-    e1.record()
-    barrier()
+    rep_ms = []
+    t_wall = time.perf_counter()
+    while True:
+        e0 = torch.cuda.Event(enable_timing=True)
+        e1 = torch.cuda.Event(enable_timing=True)
+        barrier()
+        e0.record()
+        for i in range(args.steps):
+            step()
+        e1.record()
+        barrier()
+        t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        rep_ms.append(float(t.item()))
+        go = torch.tensor([1.0 if (time.perf_counter() - t_wall < MIN_TIMED_S or len(rep_ms) < MIN_REPS) else 0.0],
+                          dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.broadcast(go, 0)                              # every rank runs the same number of repetitions
+        if go.item() == 0.0 or len(rep_ms) >= 400:
+            break
     sampler.mark_end()
-    ms_total = e0.elapsed_time(e1)
+    n_reps = len(rep_ms)
+    launches = (ctx.launch_count - launches0) // n_reps
+    ms_total = sorted(rep_ms)[n_reps // 2]
     # per-launch durations of every kernel launched inside the timed region (events on the
-    # launching stream, recorded by the library around each launch)
+    # launching stream, recorded by the library around each launch; the most recent 8192)
     per_kernel = {}
     for kind, level, ms in ctx.get_timing():
         per_kernel.setdefault((kind, level), []).append(ms)
@@ -279,11 +337,7 @@ def run_ours(args):
         else:
             pyr_ms.append(ms)
     ctx.set_timing(False)
-    launches = ctx.launch_count - launches0
-    t = torch.tensor([ms_total], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_total = float(t.item())
+    n_timed_steps = max(len(lvl0_ms), 1)                      # one level-0 launch per step
     value = world * pairs * args.steps / (ms_total * 1e-3)
 
     # ---- end-to-end through the host-pointer stream call --------------------------------------
@@ -363,6 +417,20 @@ def run_ours(args):
             r1 = {"value": world * pairs * r1_steps / (float(t.item()) * 1e-3), "unit": UNIT, "steps": r1_steps,
                   "level0_launch_ms": sum(l0s) / len(l0s) if l0s else None,
                   "note": "same workload with the reference's own 3x3 window (get_Sum9), bit-exact kernel"}
+            c1.set_timing(False)
+            # ... and end to end through the host-pointer stream call, like `e2e`
+            c1.flow_stream(fin, LEVELS, out_u=hu, out_v=hv)
+            barrier()
+            t0 = time.perf_counter()
+            for _ in range(e2e_steps):
+                c1.flow_stream(fin, LEVELS, out_u=hu, out_v=hv)
+            torch.cuda.synchronize()
+            t = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+            if world > 1:
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            r1["e2e"] = {"value": world * pairs * e2e_steps / float(t.item()), "unit": UNIT,
+                         "h2d_bytes_per_step": (pairs + 1) * frame_bytes, "d2h_bytes_per_step": 2 * pairs * frame_bytes,
+                         "api": "of_ctf_f64_stream, win_radius = 1"}
 
     if rank == 0:
         peak, peak_src = measured_peaks()
@@ -370,22 +438,28 @@ def run_ours(args):
             r1["level0_frac"] = level0_bytes_per_pair(W, H, LEVELS) * pairs / (r1["level0_launch_ms"] * 1e-3) / 1e9 / peak
             r1["whole_path_frac"] = algorithmic_bytes_per_pair(W, H, LEVELS) * (r1["value"] / world) / (peak * 1e9)
         l0 = sum(lvl0_ms) / len(lvl0_ms) if lvl0_ms else None
+        n_sm = torch.cuda.get_device_properties(dev).multi_processor_count
         roof = None
         if l0:
             achieved = level0_bytes_per_pair(W, H, LEVELS) * pairs / (l0 * 1e-3) / 1e9
-            traffic = None
-            tp = os.path.join(ROOT, "profiles", "traffic.json")
-            if os.path.exists(tp):
-                try:
-                    traffic = json.load(open(tp)).get("level0_r%d_bytes_per_launch" % radius)
-                except Exception:
-                    traffic = None
-            roof = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                    "traffic": traffic, "peak_source": peak_src, "kernel": "lk_level (level 0, fused)",
+            # DRAM bytes of one level-0 launch: ncu cannot run inside the bench, so the figure is the
+            # committed ncu reading of this kernel at this batch size (profiles/traffic.json); null when
+            # the batch size or configuration differs from the recorded one
+            traffic, traffic_src = None, None
+            rec = recorded("traffic.json")
+            if rec and rec.get("config") == args.config and rec.get("pairs") == pairs:
+                traffic = rec.get("level0_r%d_bytes_per_launch" % radius)
+                traffic_src = rec.get("source")
+            f64 = fp64_roofline(radius, W * H * pairs, l0, clocks.get("sm_mhz"), n_sm)
+            hbm_frac = achieved / peak
+            roof = {"bound": "fp64" if f64 and f64["frac"] > hbm_frac else "hbm",
+                    "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": hbm_frac,
+                    "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
+                    "fp64": f64, "kernel": "lk_level (level 0, fused)",
                     "launch_ms": l0, "algorithmic_bytes_per_launch": level0_bytes_per_pair(W, H, LEVELS) * pairs,
                     "whole_path_frac": algorithmic_bytes_per_pair(W, H, LEVELS) * (value / world) / (peak * 1e9),
-                    "kernel_ms_per_step": {"level0": l0, "coarser_levels": sum(lvl_ms) / args.steps,
-                                           "pyr_down": sum(pyr_ms) / args.steps}}
+                    "kernel_ms_per_step": {"level0": l0, "coarser_levels": sum(lvl_ms) / n_timed_steps,
+                                           "pyr_down": sum(pyr_ms) / n_timed_steps}}
         if roof:
             # bytes-per-pixel roofline of every kernel of the step: fused level kernel of level l
             # 32 B per level-l pixel (+ 16 B per coarser pixel), pyrDown producing level l 8 B read per source
@@ -394,7 +468,7 @@ def run_ours(args):
             table = []
             for (kind, level), v in sorted(per_kernel.items()):
                 ms_launch = sum(v) / len(v)
-                launches_per_step = len(v) / args.steps
+                launches_per_step = len(v) / n_timed_steps
                 if kind == 1:
                     b = (32 * n[level] + (16 * n[level + 1] if level < LEVELS - 1 else 0)) * pairs
                     name = "lk_level L%d" % level
@@ -407,23 +481,26 @@ def run_ours(args):
             roof["per_kernel"] = table
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
-            v, cores, secs = cpu_baseline_run(frames_h, 64)
+            n_cpu = 64 if W * H <= 1920 * 1080 else 16           # about 10-15 s of CPU work
+            v, cores, secs = cpu_baseline_run(frames_h, n_cpu, radius=radius)
             from oracle import c_oracle as CO
             CO.set_threads(8)                  # the reference's hard-coded team size (ParallelVideoPyr.cpp:164)
+            n8t = 8 if W * H <= 1920 * 1080 else 4
             t0 = time.perf_counter()
-            for k in range(8):
-                CO.coarse_to_fine(frames_h[k], frames_h[k + 1], LEVELS, RADIUS)
-            v8 = 8 / (time.perf_counter() - t0)
+            for k in range(n8t):
+                CO.coarse_to_fine(frames_h[k], frames_h[k + 1], LEVELS, radius)
+            v8 = n8t / (time.perf_counter() - t0)
             cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "value_8_threads": v8,
-                   "sample": "64 pairs (the first 16 consecutive pairs of the same synthetic 1080p stream, L=3, r=%d, "
-                             "four times over), oracle/lk_oracle.c C+OpenMP port of the reference path, all host "
-                             "threads, %.1f s" % (RADIUS, secs)}
+                   "sample": "%d pairs (the first %d consecutive pairs of the same synthetic stream, L=%d, r=%d, cycled), "
+                             "oracle/lk_oracle.c C+OpenMP port of the reference path, all host threads, %.1f s"
+                             % (n_cpu, pairs, LEVELS, radius, secs)}
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_total / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": "synthetic 1920x1080 grayscale video, 3-level pyramid, 15x15 window (r=%d), "
-                                   "%d consecutive frame pairs per step per GPU" % (radius, pairs),
+            "timed": {"repetitions": n_reps, "steps_per_repetition": args.steps, "reported": "median repetition",
+                      "rep_ms_min": min(rep_ms), "rep_ms_max": max(rep_ms), "min_timed_s": MIN_TIMED_S},
+            "config": {"workload": WORKLOAD, "name": args.config,
                        "width": W, "height": H, "levels": LEVELS, "win_radius": radius, "pairs_per_step": pairs,
                        "l2": "inputs+outputs per step (%.0f MB) exceed the 126 MB L2; no flush" %
                              (((pairs + 1) + 2 * pairs) * frame_bytes / 1e6),
@@ -456,10 +533,20 @@ def main():
     ap.add_argument("--steps", type=int, default=300)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--pairs", type=int, default=PAIRS)
-    ap.add_argument("--radius", type=int, default=RADIUS)
+    ap.add_argument("--config", default="1080p", choices=sorted(CONFIGS),
+                    help="1080p = BASELINE.json configs[3] (the metric's configuration), 4k = configs[4]")
+    ap.add_argument("--pairs", type=int, default=None, help="frame pairs per step per GPU (default: the configuration's)")
+    ap.add_argument("--radius", type=int, default=None)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
+    global W, H, LEVELS, RADIUS, PAIRS, METRIC, WORKLOAD, REF_PAIRS
+    c = CONFIGS[args.config]
+    W, H, LEVELS, RADIUS, PAIRS, METRIC, REF_PAIRS = c["w"], c["h"], c["levels"], c["radius"], c["pairs"], c["metric"], c["ref_pairs"]
+    if args.pairs is None:
+        args.pairs = PAIRS
+    if args.radius is None:
+        args.radius = RADIUS
+    WORKLOAD = c["workload"].replace("15x15 window (r=7)", "%dx%d window (r=%d)" % (2 * args.radius + 1, 2 * args.radius + 1, args.radius))
     # torchrun exports OMP_NUM_THREADS=1; the CPU legs (reference arm, cpu_baseline) are to use every
     # host thread, and libgomp reads the variable when it is loaded, so set it before anything imports it
     os.environ["OMP_NUM_THREADS"] = str(host_threads())
