@@ -254,6 +254,13 @@ OF_API of_status of_mgpu_ctf_u8_stream(of_mgpu *m, const unsigned char *frames, 
 /* Number of kernel launches issued through this context since creation (bench evidence). */
 OF_API unsigned long long of_ctx_launch_count(const of_ctx *ctx);
 
+/* Small batches (up to 4 Mpixel per call: the harness pair, one 1080p pair -- the reference's own call
+ * pattern, one coarseToFineEstimation per frame, ParallelVideoPyr.cpp:831-832) are launch-bound.  The
+ * second time a call repeats exactly (same geometry, parameters and pointers) its launch sequence is
+ * captured into a CUDA graph and replayed from then on; kernels launched through a replay count in
+ * of_ctx_launch_count.  This returns the number of replays (environment OF_B200_GRAPH=0 disables them). */
+OF_API unsigned long long of_ctx_graph_replay_count(const of_ctx *ctx);
+
 #ifdef __cplusplus
 }
 #endif

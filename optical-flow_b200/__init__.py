@@ -30,7 +30,7 @@ EXPORTS = (
     "of_ctf_f64_batch_dev", "of_gesture_stats_dev", "of_pyr_down_f64_dev",
     "of_ctx_synchronize", "of_ctx_launch_count", "of_ctx_set_timing", "of_ctx_get_timing",
     "of_bgr2gray_u8_dev", "of_live_diff_f64_dev", "of_live_diff_f64", "of_ctf_u8_stream",
-    "of_ctx_get_level_f64",
+    "of_ctx_get_level_f64", "of_ctx_graph_replay_count",
     "of_mgpu_create", "of_mgpu_destroy", "of_mgpu_device_count", "of_mgpu_context", "of_mgpu_last_error_string",
     "of_mgpu_partition", "of_mgpu_ctf_f64_stream", "of_mgpu_ctf_u8_stream",
 )
@@ -115,6 +115,8 @@ def lib():
     L.of_ctx_synchronize.argtypes = [vp]
     L.of_ctx_launch_count.argtypes = [vp]
     L.of_ctx_launch_count.restype = C.c_ulonglong
+    L.of_ctx_graph_replay_count.argtypes = [vp]
+    L.of_ctx_graph_replay_count.restype = C.c_ulonglong
     L.of_ctx_set_timing.argtypes = [vp, ci]
     L.of_ctx_get_timing.argtypes = [vp, ci, vp, vp, vp, vp]
     _ = dbl
@@ -211,6 +213,10 @@ class Context:
     @property
     def launch_count(self) -> int:
         return int(lib().of_ctx_launch_count(self._h))
+
+    @property
+    def graph_replays(self) -> int:
+        return int(lib().of_ctx_graph_replay_count(self._h))
 
     def synchronize(self):
         self._check(lib().of_ctx_synchronize(self._h))

@@ -627,6 +627,7 @@ __device__ __forceinline__ void solve_pair(const LevelArgs& a, const PGeo& g, do
         fast = (div2_fast(nus[q], nvs[q], dets[q], lu[q], lv[q]) || !ok) && fast;
     }
     if (!fast) {                                         // rare: exponent range outside the fast path
+#ifdef PH_DIV_PER_QUOTIENT
 #pragma unroll
         for (int q = 0; q < 2; ++q) {
             if ((okbits >> q) & 1u) {
@@ -634,6 +635,10 @@ __device__ __forceinline__ void solve_pair(const LevelArgs& a, const PGeo& g, do
                 lv[q] = ddiv_slow(nvs[q], dets[q]);
             }
         }
+#else
+        const Quot4 q4 = div4_slow(nus[0], nvs[0], dets[0], nus[1], nvs[1], dets[1]);
+        lu[0] = q4.u0; lv[0] = q4.v0; lu[1] = q4.u1; lv[1] = q4.v1;
+#endif
     }
     double fu[2], fv[2];
 #pragma unroll

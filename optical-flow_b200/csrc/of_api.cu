@@ -38,6 +38,30 @@ struct Arena {
 
 }  // namespace
 
+// A captured launch sequence, keyed on everything that ends up in a kernel parameter.
+struct GraphKey {
+    int n_pairs, w, h, L, radius, count_thresh;
+    double det_eps, mag_thresh;
+    const void *img1, *img2, *u, *v, *mask, *stats;
+    size_t img_pair_stride, step, uv_pair_stride, uv_step, mask_pair_stride, mask_step;
+    const void* scratch;
+    bool operator==(const GraphKey& o) const
+    {
+        return n_pairs == o.n_pairs && w == o.w && h == o.h && L == o.L && radius == o.radius &&
+               count_thresh == o.count_thresh && det_eps == o.det_eps && mag_thresh == o.mag_thresh && img1 == o.img1 &&
+               img2 == o.img2 && u == o.u && v == o.v && mask == o.mask && stats == o.stats &&
+               img_pair_stride == o.img_pair_stride && step == o.step && uv_pair_stride == o.uv_pair_stride &&
+               uv_step == o.uv_step && mask_pair_stride == o.mask_pair_stride && mask_step == o.mask_step &&
+               scratch == o.scratch;
+    }
+};
+struct GraphEntry {
+    GraphKey key{};
+    cudaGraphExec_t exec = nullptr;
+    bool seen = false;
+    unsigned long long launches = 0, last_use = 0;
+};
+
 struct of_ctx {
     int device = 0;
     of_params params{};
@@ -53,6 +77,9 @@ struct of_ctx {
     size_t h_stats_cap = 0;               // (a copy into pageable memory would block the host thread)
     std::string err;
     unsigned long long launches = 0;
+    std::vector<GraphEntry> graphs;    // at most 8, least recently used replaced
+    unsigned long long graph_clock = 0, graph_replays = 0;
+    int graph_mode = 1;                // 0 never, 1 small batches, 2 always (OF_B200_GRAPH, test hook)
     int force_variant = 0;             // 0 auto, 1 tile, 4 phase (test hook via OF_B200_VARIANT)
     // optional per-launch device timing of the most recent batch call (bench roofline evidence)
     bool timing = false;
@@ -93,9 +120,45 @@ of_status fail(of_ctx* ctx, of_status code, const char* fmt, ...)
                         "%s failed: %s", #call, cudaGetErrorString(e_));                    \
     } while (0)
 
+void graph_clear(of_ctx* ctx)
+{
+    for (GraphEntry& e : ctx->graphs)
+        if (e.exec) cudaGraphExecDestroy(e.exec);
+    ctx->graphs.clear();
+}
+
+bool graph_eligible(const of_ctx* ctx, int n_pairs, int w, int h)
+{
+    if (ctx->timing || ctx->graph_mode == 0) return false;       // per-launch timing needs the launches themselves
+    return ctx->graph_mode == 2 || (long long)n_pairs * w * h <= (1ll << 22);
+}
+
+GraphEntry* graph_lookup(of_ctx* ctx, const GraphKey& key)
+{
+    ctx->graph_clock += 1;
+    for (GraphEntry& e : ctx->graphs)
+        if (e.key == key) {
+            e.last_use = ctx->graph_clock;
+            return &e;
+        }
+    if (ctx->graphs.size() >= 8) {
+        size_t victim = 0;
+        for (size_t i = 1; i < ctx->graphs.size(); ++i)
+            if (ctx->graphs[i].last_use < ctx->graphs[victim].last_use) victim = i;
+        if (ctx->graphs[victim].exec) cudaGraphExecDestroy(ctx->graphs[victim].exec);
+        ctx->graphs.erase(ctx->graphs.begin() + victim);
+    }
+    GraphEntry e;
+    e.key = key;
+    e.last_use = ctx->graph_clock;
+    ctx->graphs.push_back(e);
+    return &ctx->graphs.back();
+}
+
 of_status arena_reserve(of_ctx* ctx, Arena& a, size_t bytes)
 {
     if (bytes <= a.cap) return OF_OK;
+    if (&a == &ctx->scratch) graph_clear(ctx);                   // captured launches point into the old arena
     if (a.base) {
         OF_CUDA(ctx, cudaDeviceSynchronize());
         OF_CUDA(ctx, cudaFree(a.base));
@@ -255,50 +318,14 @@ cudaError_t launch_lk_level(of_ctx* ctx, const ofb::LevelArgs& a, int n_pairs, c
     return ofb::launch_lk_level_tile(a, n_pairs, s, &ctx->launches);
 }
 
-// Core: all device pointers, stream-ordered.
-of_status run_batch(of_ctx* ctx, int n_pairs, const double* img1, const double* img2,
-                    size_t img_pair_stride, int w, int h, size_t step, int L, double* u,
-                    double* v, size_t uv_pair_stride, size_t uv_step, unsigned char* mask,
-                    size_t mask_pair_stride, size_t mask_step, of_gesture_stats* stats,
-                    cudaStream_t s)
+// The launch sequence of one batch on stream s: pyramids, then one fused kernel per level, coarse to fine.
+of_status enqueue_batch(of_ctx* ctx, const Plan& p, int n_pairs, const double* img1, const double* img2, size_t in_pitch,
+                        size_t in_stride, int L, double* u, double* v, size_t uv_pair_stride, size_t uv_step,
+                        unsigned char* mask, size_t mask_pair_stride, size_t mask_step, of_gesture_stats* stats,
+                        cudaStream_t s)
 {
-    of_status st = check_common(ctx, img1, img2, w, h, step, L);
-    if (st) return st;
-    if (n_pairs < 1) return fail(ctx, OF_E_BADARG, "n_pairs must be >= 1");
-    if ((u == nullptr) != (v == nullptr)) return fail(ctx, OF_E_BADARG, "u and v must both be given or both be NULL");
-    if (!u && !stats && !mask) return fail(ctx, OF_E_BADARG, "nothing to compute: u, v, mask and stats are all NULL");
-    if (u && (uv_step % sizeof(double) || uv_step < (size_t)w * sizeof(double)))
-        return fail(ctx, OF_E_BADARG, "uv_step_bytes %zu invalid for width %d", uv_step, w);
-    if (mask && mask_step < (size_t)w) return fail(ctx, OF_E_BADARG, "mask_step_bytes %zu < width", mask_step);
-    if (mask && n_pairs > 1 && mask_pair_stride < mask_step * (size_t)(h - 1) + (size_t)w)
-        return fail(ctx, OF_E_BADARG, "mask_pair_stride_bytes %zu is smaller than one mask plane", mask_pair_stride);
-    if (u && n_pairs > 1 && uv_pair_stride < uv_step * (size_t)(h - 1) + (size_t)w * sizeof(double))
-        return fail(ctx, OF_E_BADARG, "uv_pair_stride_bytes %zu is smaller than one flow plane", uv_pair_stride);
-    if (n_pairs > 1 && img_pair_stride % sizeof(double))
-        return fail(ctx, OF_E_BADARG, "img_pair_stride_bytes must be a multiple of 8");
-    if (u && n_pairs > 1 && uv_pair_stride % sizeof(double))
-        return fail(ctx, OF_E_BADARG, "uv_pair_stride_bytes must be a multiple of 8");
-    if (ctx->params.win_radius < 1 || ctx->params.win_radius > 15)
-        return fail(ctx, OF_E_BADARG, "win_radius must be in 1..15");
-    OF_CUDA(ctx, cudaSetDevice(ctx->device));
-    // scratch hand-over between streams (see of_ctx::ev_scratch)
-    if (ctx->scratch_busy && ctx->last_stream != s) OF_CUDA(ctx, cudaStreamWaitEvent(s, ctx->ev_scratch, 0));
-
-    const bool shared = n_pairs > 1 && (const char*)img2 == (const char*)img1 + img_pair_stride;
-    Plan p = make_plan(w, h, L, n_pairs, shared, u == nullptr);
-    st = arena_reserve(ctx, ctx->scratch, p.total);
-    if (st) return st;
     char* base = ctx->scratch.base;
-    const size_t in_pitch = step / sizeof(double);
-    const size_t in_stride = img_pair_stride / sizeof(double);
-    ctx->last.assign(L, of_ctx::LastLevel{});
-    for (int l = 0; l < L; ++l)
-        ctx->last[l] = {p.g[l].w, p.g[l].h, p.g[l].pitch, p.g[l].img_stride, l ? p.pyr_off[l] : 0,
-                        l ? p.flow_u_off[l] : 0, l ? p.flow_v_off[l] : 0};
-    ctx->last_pairs = n_pairs;
-    ctx->last_shared = shared;
-    ctx->last_stream = s;
-
+    const bool shared = p.shared;
     // ---- Gaussian pyramids (getGaussianPyramid :566-575, both frames :587-597) ------------
     for (int l = 1; l < L; ++l) {
         const LevelGeom& gs = p.g[l - 1];
@@ -397,6 +424,95 @@ of_status run_batch(of_ctx* ctx, int n_pairs, const double* img1, const double* 
     }
     if (stats)
         OF_CUDA(ctx, ofb::launch_stats_finalize(stats, n_pairs, (double)ctx->params.count_thresh, s, &ctx->launches));
+    return OF_OK;
+}
+
+// Core: all device pointers, stream-ordered.
+of_status run_batch(of_ctx* ctx, int n_pairs, const double* img1, const double* img2,
+                    size_t img_pair_stride, int w, int h, size_t step, int L, double* u,
+                    double* v, size_t uv_pair_stride, size_t uv_step, unsigned char* mask,
+                    size_t mask_pair_stride, size_t mask_step, of_gesture_stats* stats,
+                    cudaStream_t s)
+{
+    of_status st = check_common(ctx, img1, img2, w, h, step, L);
+    if (st) return st;
+    if (n_pairs < 1) return fail(ctx, OF_E_BADARG, "n_pairs must be >= 1");
+    if ((u == nullptr) != (v == nullptr)) return fail(ctx, OF_E_BADARG, "u and v must both be given or both be NULL");
+    if (!u && !stats && !mask) return fail(ctx, OF_E_BADARG, "nothing to compute: u, v, mask and stats are all NULL");
+    if (u && (uv_step % sizeof(double) || uv_step < (size_t)w * sizeof(double)))
+        return fail(ctx, OF_E_BADARG, "uv_step_bytes %zu invalid for width %d", uv_step, w);
+    if (mask && mask_step < (size_t)w) return fail(ctx, OF_E_BADARG, "mask_step_bytes %zu < width", mask_step);
+    if (mask && n_pairs > 1 && mask_pair_stride < mask_step * (size_t)(h - 1) + (size_t)w)
+        return fail(ctx, OF_E_BADARG, "mask_pair_stride_bytes %zu is smaller than one mask plane", mask_pair_stride);
+    if (u && n_pairs > 1 && uv_pair_stride < uv_step * (size_t)(h - 1) + (size_t)w * sizeof(double))
+        return fail(ctx, OF_E_BADARG, "uv_pair_stride_bytes %zu is smaller than one flow plane", uv_pair_stride);
+    if (n_pairs > 1 && img_pair_stride % sizeof(double))
+        return fail(ctx, OF_E_BADARG, "img_pair_stride_bytes must be a multiple of 8");
+    if (u && n_pairs > 1 && uv_pair_stride % sizeof(double))
+        return fail(ctx, OF_E_BADARG, "uv_pair_stride_bytes must be a multiple of 8");
+    if (ctx->params.win_radius < 1 || ctx->params.win_radius > 15)
+        return fail(ctx, OF_E_BADARG, "win_radius must be in 1..15");
+    OF_CUDA(ctx, cudaSetDevice(ctx->device));
+    // scratch hand-over between streams (see of_ctx::ev_scratch)
+    if (ctx->scratch_busy && ctx->last_stream != s) OF_CUDA(ctx, cudaStreamWaitEvent(s, ctx->ev_scratch, 0));
+
+    const bool shared = n_pairs > 1 && (const char*)img2 == (const char*)img1 + img_pair_stride;
+    Plan p = make_plan(w, h, L, n_pairs, shared, u == nullptr);
+    st = arena_reserve(ctx, ctx->scratch, p.total);
+    if (st) return st;
+    char* base = ctx->scratch.base;
+    const size_t in_pitch = step / sizeof(double);
+    const size_t in_stride = img_pair_stride / sizeof(double);
+    ctx->last.assign(L, of_ctx::LastLevel{});
+    for (int l = 0; l < L; ++l)
+        ctx->last[l] = {p.g[l].w, p.g[l].h, p.g[l].pitch, p.g[l].img_stride, l ? p.pyr_off[l] : 0,
+                        l ? p.flow_u_off[l] : 0, l ? p.flow_v_off[l] : 0};
+    ctx->last_pairs = n_pairs;
+    ctx->last_shared = shared;
+    ctx->last_stream = s;
+
+    // Small batches are launch-bound (KAT-7: 14 launches for 21 MB; the live loop calls one pair at a
+    // time, :831-832): their launch sequence is captured into a CUDA graph the second time the same
+    // call (geometry, parameters and pointers) is made, and replayed from then on.
+    GraphKey key{};
+    GraphEntry* ge = nullptr;
+    if (graph_eligible(ctx, n_pairs, w, h)) {
+        key = {n_pairs, w, h, L, ctx->params.win_radius, ctx->params.count_thresh, ctx->params.det_eps, ctx->params.mag_thresh,
+               img1, img2, u, v, mask, stats, img_pair_stride, step, uv_pair_stride, uv_step, mask_pair_stride, mask_step,
+               ctx->scratch.base};
+        ge = graph_lookup(ctx, key);
+    }
+    if (ge && ge->exec) {
+        OF_CUDA(ctx, cudaGraphLaunch(ge->exec, s));
+        ctx->launches += ge->launches;
+        ctx->graph_replays += 1;
+    } else if (ge && ge->seen) {
+        // second sighting: capture on the context's own stream (a legacy default stream cannot capture)
+        const unsigned long long l0 = ctx->launches;
+        OF_CUDA(ctx, cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeRelaxed));
+        st = enqueue_batch(ctx, p, n_pairs, img1, img2, in_pitch, in_stride, L, u, v, uv_pair_stride, uv_step, mask,
+                           mask_pair_stride, mask_step, stats, ctx->stream);
+        cudaGraph_t g = nullptr;
+        cudaError_t e = cudaStreamEndCapture(ctx->stream, &g);
+        if (st) {
+            if (g) cudaGraphDestroy(g);
+            return st;
+        }
+        if (e == cudaSuccess) e = cudaGraphInstantiate(&ge->exec, g, 0);
+        if (g) cudaGraphDestroy(g);
+        if (e != cudaSuccess) {
+            ge->exec = nullptr;
+            return fail(ctx, OF_E_CUDA, "CUDA graph capture failed: %s", cudaGetErrorString(e));
+        }
+        ge->launches = ctx->launches - l0;
+        OF_CUDA(ctx, cudaGraphLaunch(ge->exec, s));
+        ctx->graph_replays += 1;
+    } else {
+        if (ge) ge->seen = true;
+        st = enqueue_batch(ctx, p, n_pairs, img1, img2, in_pitch, in_stride, L, u, v, uv_pair_stride, uv_step, mask,
+                           mask_pair_stride, mask_step, stats, s);
+        if (st) return st;
+    }
     OF_CUDA(ctx, cudaEventRecord(ctx->ev_scratch, s));
     ctx->scratch_busy = true;
     return OF_OK;
@@ -467,6 +583,7 @@ of_status of_ctx_create(int device, const of_params* params, of_ctx** out)
         }
         ctx->params = *params;
     }
+    if (const char* gm = getenv("OF_B200_GRAPH")) ctx->graph_mode = atoi(gm);
     if (const char* fv = getenv("OF_B200_VARIANT")) {
         if (!strcmp(fv, "tile")) ctx->force_variant = 1;
         else if (!strcmp(fv, "phase")) ctx->force_variant = 4;
@@ -495,6 +612,7 @@ void of_ctx_destroy(of_ctx* ctx)
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     cudaDeviceSynchronize();
+    graph_clear(ctx);
     if (ctx->scratch.base) cudaFree(ctx->scratch.base);
     if (ctx->staging.base) cudaFree(ctx->staging.base);
     if (ctx->h_stats) cudaFreeHost(ctx->h_stats);
@@ -522,6 +640,8 @@ of_status of_ctx_set_params(of_ctx* ctx, const of_params* params)
 const char* of_last_error_string(const of_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
 
 unsigned long long of_ctx_launch_count(const of_ctx* ctx) { return ctx ? ctx->launches : 0ull; }
+
+unsigned long long of_ctx_graph_replay_count(const of_ctx* ctx) { return ctx ? ctx->graph_replays : 0ull; }
 
 of_status of_ctx_set_timing(of_ctx* ctx, int enable)
 {

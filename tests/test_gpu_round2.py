@@ -113,6 +113,48 @@ def test_calls_on_different_streams_are_ordered(ofb, c_oracle):
     assert np.abs(U[7].cpu().numpy() - want7[0]).max() <= FLOW_TOL
 
 
+def test_repeated_small_calls_replay_a_cuda_graph(ofb, c_oracle, table_pair, monkeypatch):
+    """The reference's call pattern (one pair per call, same buffers): from the third identical call on the
+    launch sequence is a graph replay; results stay those of the plain launches; new pointers, new
+    parameters or a larger scratch arena never replay a stale graph."""
+    import torch
+    a, b = table_pair
+    d = torch.from_numpy(np.stack([a, b])).cuda()
+    u = torch.empty((448, 640), dtype=torch.float64, device="cuda")
+    v = torch.empty_like(u)
+    want = c_oracle.coarse_to_fine(a, b, 7)
+    with ofb.Context(0) as ctx:
+        n0 = ctx.launch_count
+        for k in range(5):
+            u.zero_()
+            ctx.coarseToFineEstimation_dev(d[0], d[1], 7, u, v)
+            torch.cuda.synchronize()
+            assert np.array_equal(u.cpu().numpy(), want[0]) and np.array_equal(v.cpu().numpy(), want[1]), k
+        assert ctx.graph_replays == 4                       # calls 2..5 (the second one captures, then replays)
+        per_call = (ctx.launch_count - n0) // 5
+        assert per_call >= 13 and (ctx.launch_count - n0) == 5 * per_call
+        u2 = torch.empty_like(u)                            # other pointers: plain launches again
+        ctx.coarseToFineEstimation_dev(d[0], d[1], 7, u2, v)
+        assert ctx.graph_replays == 4
+        ctx.set_params(win_radius=2)                        # other parameters
+        ctx.coarseToFineEstimation_dev(d[0], d[1], 7, u, v)
+        assert ctx.graph_replays == 4
+        ctx.set_params(win_radius=1)
+        big = torch.zeros((2, 1024, 2048), dtype=torch.float64, device="cuda")      # grows the arena: graphs dropped
+        ub = torch.empty((1024, 2048), dtype=torch.float64, device="cuda")
+        ctx.coarseToFineEstimation_dev(big[0], big[1], 3, ub, ub.clone())
+        for k in range(3):
+            ctx.coarseToFineEstimation_dev(d[0], d[1], 7, u, v)
+        torch.cuda.synchronize()
+        assert ctx.graph_replays == 6
+        assert np.array_equal(u.cpu().numpy(), want[0])
+    monkeypatch.setenv("OF_B200_GRAPH", "0")
+    with ofb.Context(0) as ctx:
+        for k in range(3):
+            ctx.coarseToFineEstimation_dev(d[0], d[1], 7, u, v)
+        assert ctx.graph_replays == 0
+
+
 def test_write_back_rejected_where_inputs_are_const(ofb):
     import torch
     z = torch.zeros((2, 64, 64), dtype=torch.float64, device="cuda")
