@@ -205,6 +205,49 @@ OF_API of_status of_live_diff_f64(of_ctx *ctx, const unsigned char *cur, const u
                            int coeff_bits, double learning_rate, int diff_thresh,
                            int morph_iterations, double *out, size_t out_step_bytes);
 
+/* Replaces: resize(frame, current_frame, Size(1080, 1080), 0, 0, INTER_CUBIC)   ParallelVideoPyr.cpp:782.
+ * 8-bit, `channels` = 1 or 3 interleaved; cv::resize's fixed-point bicubic (A = -0.75, 11-bit
+ * coefficients, BORDER_REPLICATE taps) as cv2 4.13 computes it without IPP.  Equal sizes copy.  Device
+ * pointers; the coefficient tables are cached in the context per geometry. */
+OF_API of_status of_resize_cubic_u8_dev(of_ctx *ctx, const unsigned char *src, int src_width, int src_height,
+                                 size_t src_step_bytes, int channels, unsigned char *dst, int dst_width,
+                                 int dst_height, size_t dst_step_bytes, void *stream);
+
+/* Replaces: GaussianBlur(current_frame, current_frame, Size(9, 9), 1.5, 1.5)   ParallelVideoPyr.cpp:790
+ * (+ optionally cvtColor(CV_BGR2GRAY) :791 fused: gray_coeff_bits = 14 / 15 with channels = 3 writes one
+ * gray channel; 0 writes the blurred image).  8-bit fixed point: integer kernel / 256 in both passes
+ * (for 9 / 1.5: 2 9 28 55 68 55 28 9 2), BORDER_REFLECT_101, (sum + 2^15) >> 16.  ksize odd, <= 31.
+ * src and dst must not overlap.  Device pointers. */
+OF_API of_status of_gaussian_blur_u8_dev(of_ctx *ctx, const unsigned char *src, int width, int height,
+                                  size_t src_step_bytes, int channels, int ksize, double sigma,
+                                  int gray_coeff_bits, unsigned char *dst, size_t dst_step_bytes, void *stream);
+
+/* One iteration of the reference's live loop, headless (main(), ParallelVideoPyr.cpp:769-905, without
+ * VideoCapture / imshow / circle): the captured 8-bit BGR frame (host pointer) goes through
+ *   resize :782 -> GaussianBlur :790 -> cvtColor :791 -> cur - 0.3 prev :800 -> threshold :803 ->
+ *   Sobel x + y :808-811 -> dilate x2 / erode x2 :812-813 -> coarseToFineEstimation(prevDiff, diff) :832
+ *   -> gesture statistics :845-888
+ * entirely on the device; the context keeps prevFrame / prevDiff between calls like the loop does.
+ * *stage = 0: first frame stored (:793-797), 1: first difference image stored (:816-820), 2: *stats is
+ * valid (and u, v when given: host planes of work_width x work_height doubles, may be NULL).
+ * With of_params.write_back_warped = 1 prevDiff becomes the WARPED difference image, as in the reference
+ * (quirk Q1: coarseToFineEstimation overwrites its inputs, then prevDiff = diff :843); default: unwarped. */
+typedef struct of_live_params {
+    int work_width, work_height; /* 1080, 1080 (:782)                                               */
+    int blur_ksize;              /* 9 (:790)                                                        */
+    double blur_sigma;           /* 1.5                                                             */
+    int coeff_bits;              /* cvtColor table: 14 = OpenCV 2.4 (the reference's), 15 = OpenCV >= 3 */
+    double learning_rate;        /* 0.3  (LEARNING_RATE :729)                                       */
+    int diff_thresh;             /* 10   (DIFF_THRESH :728)                                         */
+    int morph_iterations;        /* 2    (:812-813)                                                 */
+    int n_levels;                /* 0 = getMaxLayer(work size) (:831), else the given pyramid depth */
+} of_live_params;
+OF_API void of_live_params_default(of_live_params *p);
+OF_API of_status of_live_step_u8(of_ctx *ctx, const of_live_params *lp, const unsigned char *frame_bgr,
+                          int width, int height, size_t step_bytes, of_gesture_stats *stats,
+                          double *u, double *v, size_t uv_step_bytes, int *stage);
+OF_API of_status of_live_reset(of_ctx *ctx);   /* forget prevFrame / prevDiff: the next frame is a first frame */
+
 /* Blocks until everything queued on the context's own stream has finished. */
 OF_API of_status of_ctx_synchronize(of_ctx *ctx);
 

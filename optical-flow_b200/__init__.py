@@ -31,6 +31,7 @@ EXPORTS = (
     "of_ctx_synchronize", "of_ctx_launch_count", "of_ctx_set_timing", "of_ctx_get_timing",
     "of_bgr2gray_u8_dev", "of_live_diff_f64_dev", "of_live_diff_f64", "of_ctf_u8_stream",
     "of_ctx_get_level_f64", "of_ctx_graph_replay_count",
+    "of_resize_cubic_u8_dev", "of_gaussian_blur_u8_dev", "of_live_params_default", "of_live_step_u8", "of_live_reset",
     "of_mgpu_create", "of_mgpu_destroy", "of_mgpu_device_count", "of_mgpu_context", "of_mgpu_last_error_string",
     "of_mgpu_partition", "of_mgpu_ctf_f64_stream", "of_mgpu_ctf_u8_stream",
 )
@@ -39,6 +40,12 @@ EXPORTS = (
 class OfParams(C.Structure):
     _fields_ = [("win_radius", C.c_int), ("det_eps", C.c_double), ("write_back_warped", C.c_int),
                 ("mag_thresh", C.c_double), ("count_thresh", C.c_int)]
+
+
+class OfLiveParams(C.Structure):
+    _fields_ = [("work_width", C.c_int), ("work_height", C.c_int), ("blur_ksize", C.c_int), ("blur_sigma", C.c_double),
+                ("coeff_bits", C.c_int), ("learning_rate", C.c_double), ("diff_thresh", C.c_int),
+                ("morph_iterations", C.c_int), ("n_levels", C.c_int)]
 
 
 class OfGestureStats(C.Structure):
@@ -115,6 +122,12 @@ def lib():
     L.of_ctx_synchronize.argtypes = [vp]
     L.of_ctx_launch_count.argtypes = [vp]
     L.of_ctx_launch_count.restype = C.c_ulonglong
+    L.of_resize_cubic_u8_dev.argtypes = [vp, vp, ci, ci, sz, ci, vp, ci, ci, sz, vp]
+    L.of_gaussian_blur_u8_dev.argtypes = [vp, vp, ci, ci, sz, ci, ci, dbl, ci, vp, sz, vp]
+    L.of_live_params_default.argtypes = [C.POINTER(OfLiveParams)]
+    L.of_live_params_default.restype = None
+    L.of_live_step_u8.argtypes = [vp, C.POINTER(OfLiveParams), vp, ci, ci, sz, vp, vp, vp, sz, C.POINTER(ci)]
+    L.of_live_reset.argtypes = [vp]
     L.of_ctx_graph_replay_count.argtypes = [vp]
     L.of_ctx_graph_replay_count.restype = C.c_ulonglong
     L.of_ctx_set_timing.argtypes = [vp, ci]
@@ -406,6 +419,50 @@ class Context:
                                            coeff_bits, learning_rate, diff_thresh, morph_iterations,
                                            out.ctypes.data, w * 8))
         return out
+
+    def resize_cubic_dev(self, src, dst, stream=None):
+        """cv::resize(INTER_CUBIC) :782 on device tensors: src (H, W[, 3]) uint8 -> dst (H2, W2[, 3]) uint8."""
+        cn = 1 if src.dim() == 2 else src.shape[2]
+        s = _stream_handle(stream, src.device)
+        self._check(lib().of_resize_cubic_u8_dev(self._h, src.data_ptr(), src.shape[1], src.shape[0], src.stride(0), cn,
+                                                 dst.data_ptr(), dst.shape[1], dst.shape[0], dst.stride(0), s))
+
+    def gaussian_blur_dev(self, src, dst, ksize: int = 9, sigma: float = 1.5, gray_coeff_bits: int = 0, stream=None):
+        """cv::GaussianBlur :790 on device tensors (uint8, (H, W) or (H, W, 3)); gray_coeff_bits = 14 / 15 fuses
+        cvtColor(BGR2GRAY) :791 and writes an (H, W) gray image."""
+        cn = 1 if src.dim() == 2 else src.shape[2]
+        s = _stream_handle(stream, src.device)
+        self._check(lib().of_gaussian_blur_u8_dev(self._h, src.data_ptr(), src.shape[1], src.shape[0], src.stride(0), cn,
+                                                  int(ksize), float(sigma), int(gray_coeff_bits), dst.data_ptr(),
+                                                  dst.stride(0), s))
+
+    def live_reset(self):
+        self._check(lib().of_live_reset(self._h))
+
+    def live_step(self, frame_bgr, want_flow: bool = False, **kw):
+        """One iteration of the reference's live loop (main(), :769-905) on a captured 8-bit BGR frame (host
+        array (H, W, 3)); keyword arguments override of_live_params (work_width, work_height, blur_ksize,
+        blur_sigma, coeff_bits, learning_rate, diff_thresh, morph_iterations, n_levels).
+        Returns (stage, stats, u, v): stage 0 / 1 = warm-up iterations (no result), 2 = stats valid."""
+        f = np.ascontiguousarray(frame_bgr)
+        if f.dtype != np.uint8 or f.ndim != 3 or f.shape[2] != 3:
+            raise BadArgError(OF_E_BADARG, "frame must be an (H, W, 3) uint8 array")
+        lp = OfLiveParams()
+        lib().of_live_params_default(C.byref(lp))
+        for k, val in kw.items():
+            if not hasattr(lp, k):
+                raise BadArgError(OF_E_BADARG, "unknown live parameter %s" % k)
+            setattr(lp, k, val)
+        stats = np.zeros(1, STATS_DTYPE)
+        u = v = None
+        if want_flow:
+            u = np.empty((lp.work_height, lp.work_width), np.float64)
+            v = np.empty_like(u)
+        stage = C.c_int(-1)
+        self._check(lib().of_live_step_u8(self._h, C.byref(lp), f.ctypes.data, f.shape[1], f.shape[0], f.strides[0],
+                                          stats.ctypes.data, u.ctypes.data if want_flow else None,
+                                          v.ctypes.data if want_flow else None, lp.work_width * 8, C.byref(stage)))
+        return stage.value, (stats[0] if stage.value == 2 else None), u, v
 
     def bgr2gray_dev(self, bgr, gray, coeff_bits: int = 14, stream=None):
         """cvtColor(CV_BGR2GRAY) :791 on device tensors: bgr (H, W, 3) uint8 -> gray (H, W) uint8."""

@@ -73,6 +73,11 @@ struct of_ctx {
     cudaEvent_t ev_down[2] = {nullptr, nullptr};
     Arena scratch;                     // pyramids + per-level flows
     Arena staging;                     // device copies of host-pointer inputs/outputs
+    Arena live;                        // live loop: frame, resized frame, gray frames, difference images
+    // resize tables (device), cached per geometry
+    struct ResizeTab { int sw = 0, sh = 0, dw = 0, dh = 0; int *xofs = nullptr, *yofs = nullptr; short* xco = nullptr; float* ybeta = nullptr; } rz;
+    // live-loop state (of_live_step_u8): prevFrame / prevDiff of main() :765-766
+    struct LiveState { int w = 0, h = 0, frames = 0, cur_gray = 0, cur_diff = 0; } ls;
     of_gesture_stats* h_stats = nullptr;  // pinned host staging of the stream call's statistics
     size_t h_stats_cap = 0;               // (a copy into pageable memory would block the host thread)
     std::string err;
@@ -613,6 +618,8 @@ void of_ctx_destroy(of_ctx* ctx)
     cudaSetDevice(ctx->device);
     cudaDeviceSynchronize();
     graph_clear(ctx);
+    if (ctx->live.base) cudaFree(ctx->live.base);
+    if (ctx->rz.xofs) cudaFree(ctx->rz.xofs);
     if (ctx->scratch.base) cudaFree(ctx->scratch.base);
     if (ctx->staging.base) cudaFree(ctx->staging.base);
     if (ctx->h_stats) cudaFreeHost(ctx->h_stats);
@@ -876,6 +883,236 @@ of_status of_live_diff_f64(of_ctx* ctx, const unsigned char* cur, const unsigned
     OF_CUDA(ctx, cudaStreamSynchronize(s));
     return OF_OK;
 }
+
+}  // extern "C"
+
+/* ---- live-loop colour-frame steps and the whole iteration (ParallelVideoPyr.cpp:769-905) ---------- */
+
+namespace {
+
+// Device-resident bicubic tables for (sw, sh) -> (dw, dh), built once per geometry.
+of_status resize_tables(of_ctx* ctx, int sw, int sh, int dw, int dh)
+{
+    of_ctx::ResizeTab& t = ctx->rz;
+    if (t.xofs && t.sw == sw && t.sh == sh && t.dw == dw && t.dh == dh) return OF_OK;
+    if (t.xofs) {
+        OF_CUDA(ctx, cudaDeviceSynchronize());
+        cudaFree(t.xofs);
+        t = of_ctx::ResizeTab{};
+    }
+    std::vector<int> xo(4 * (size_t)dw), yo(4 * (size_t)dh);
+    std::vector<short> xc(4 * (size_t)dw), yc(4 * (size_t)dh);
+    std::vector<float> yb(4 * (size_t)dh);
+    ofb::build_cubic_table(sw, dw, xo.data(), xc.data());
+    ofb::build_cubic_table(sh, dh, yo.data(), yc.data());
+    const float scale = 1.0f / (2048.0f * 2048.0f);
+    for (size_t i = 0; i < yb.size(); ++i) yb[i] = (float)yc[i] * scale;
+    const size_t b_xo = align_up(xo.size() * 4, 256), b_yo = align_up(yo.size() * 4, 256);
+    const size_t b_yb = align_up(yb.size() * 4, 256), b_xc = align_up(xc.size() * 2, 256);
+    char* base = nullptr;
+    cudaError_t e = cudaMalloc((void**)&base, b_xo + b_yo + b_yb + b_xc);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return fail(ctx, OF_E_NOMEM, "cudaMalloc of the resize tables failed: %s", cudaGetErrorString(e));
+    }
+    t.xofs = (int*)base;
+    t.yofs = (int*)(base + b_xo);
+    t.ybeta = (float*)(base + b_xo + b_yo);
+    t.xco = (short*)(base + b_xo + b_yo + b_yb);
+    OF_CUDA(ctx, cudaMemcpy(t.xofs, xo.data(), xo.size() * 4, cudaMemcpyHostToDevice));
+    OF_CUDA(ctx, cudaMemcpy(t.yofs, yo.data(), yo.size() * 4, cudaMemcpyHostToDevice));
+    OF_CUDA(ctx, cudaMemcpy(t.ybeta, yb.data(), yb.size() * 4, cudaMemcpyHostToDevice));
+    OF_CUDA(ctx, cudaMemcpy(t.xco, xc.data(), xc.size() * 2, cudaMemcpyHostToDevice));
+    t.sw = sw; t.sh = sh; t.dw = dw; t.dh = dh;
+    return OF_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+of_status of_resize_cubic_u8_dev(of_ctx* ctx, const unsigned char* src, int src_width, int src_height,
+                                 size_t src_step_bytes, int channels, unsigned char* dst, int dst_width,
+                                 int dst_height, size_t dst_step_bytes, void* stream)
+{
+    if (!ctx) return OF_E_BADARG;
+    if (!src || !dst || src_width < 1 || src_height < 1 || dst_width < 1 || dst_height < 1)
+        return fail(ctx, OF_E_BADARG, "bad argument to of_resize_cubic_u8_dev");
+    if (channels != 1 && channels != 3) return fail(ctx, OF_E_BADARG, "channels must be 1 or 3");
+    if (src_step_bytes < (size_t)src_width * channels || dst_step_bytes < (size_t)dst_width * channels)
+        return fail(ctx, OF_E_BADARG, "bad step");
+    OF_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t s = pick(ctx, stream);
+    if (src_width == dst_width && src_height == dst_height) {          // cv::resize copies when the sizes agree
+        OF_CUDA(ctx, cudaMemcpy2DAsync(dst, dst_step_bytes, src, src_step_bytes, (size_t)src_width * channels, src_height,
+                                       cudaMemcpyDeviceToDevice, s));
+        return OF_OK;
+    }
+    if (of_status st = resize_tables(ctx, src_width, src_height, dst_width, dst_height)) return st;
+    OF_CUDA(ctx, ofb::launch_resize_cubic(src, src_step_bytes, channels, dst, dst_step_bytes, dst_width, dst_height,
+                                          ctx->rz.xofs, ctx->rz.xco, ctx->rz.yofs, ctx->rz.ybeta, s, &ctx->launches));
+    return OF_OK;
+}
+
+of_status of_gaussian_blur_u8_dev(of_ctx* ctx, const unsigned char* src, int width, int height, size_t src_step_bytes,
+                                  int channels, int ksize, double sigma, int gray_coeff_bits, unsigned char* dst,
+                                  size_t dst_step_bytes, void* stream)
+{
+    if (!ctx) return OF_E_BADARG;
+    if (!src || !dst || width < 1 || height < 1) return fail(ctx, OF_E_BADARG, "bad argument to of_gaussian_blur_u8_dev");
+    if (channels != 1 && channels != 3) return fail(ctx, OF_E_BADARG, "channels must be 1 or 3");
+    if (gray_coeff_bits != 0 && gray_coeff_bits != 14 && gray_coeff_bits != 15)
+        return fail(ctx, OF_E_BADARG, "gray_coeff_bits must be 0, 14 or 15");
+    if (gray_coeff_bits && channels != 3) return fail(ctx, OF_E_BADARG, "the fused cvtColor needs channels = 3");
+    if (src_step_bytes < (size_t)width * channels || dst_step_bytes < (size_t)width * (gray_coeff_bits ? 1 : channels))
+        return fail(ctx, OF_E_BADARG, "bad step");
+    int k[31];
+    if (!ofb::build_gauss_kernel_q8(ksize, sigma, k)) return fail(ctx, OF_E_BADARG, "ksize must be odd, 1..31, sigma > 0");
+    OF_CUDA(ctx, cudaSetDevice(ctx->device));
+    OF_CUDA(ctx, ofb::launch_gauss_u8(src, src_step_bytes, channels, dst, dst_step_bytes, width, height, k, ksize,
+                                      gray_coeff_bits, pick(ctx, stream), &ctx->launches));
+    return OF_OK;
+}
+
+void of_live_params_default(of_live_params* p)
+{
+    if (!p) return;
+    p->work_width = p->work_height = 1080;
+    p->blur_ksize = 9;
+    p->blur_sigma = 1.5;
+    p->coeff_bits = 14;
+    p->learning_rate = 0.3;
+    p->diff_thresh = 10;
+    p->morph_iterations = 2;
+    p->n_levels = 0;
+}
+
+of_status of_live_reset(of_ctx* ctx)
+{
+    if (!ctx) return OF_E_BADARG;
+    ctx->ls = of_ctx::LiveState{};
+    return OF_OK;
+}
+
+of_status of_live_step_u8(of_ctx* ctx, const of_live_params* lp_in, const unsigned char* frame_bgr, int width, int height,
+                          size_t step_bytes, of_gesture_stats* stats, double* u, double* v, size_t uv_step_bytes,
+                          int* stage)
+{
+    if (!ctx) return OF_E_BADARG;
+    of_live_params lp;
+    of_live_params_default(&lp);
+    if (lp_in) lp = *lp_in;
+    if (!frame_bgr || width < 1 || height < 1 || step_bytes < (size_t)width * 3)
+        return fail(ctx, OF_E_BADARG, "bad frame argument to of_live_step_u8");
+    if (!stage) return fail(ctx, OF_E_BADARG, "stage is NULL");
+    if ((u == nullptr) != (v == nullptr)) return fail(ctx, OF_E_BADARG, "u and v must both be given or both be NULL");
+    const int W = lp.work_width, H = lp.work_height;
+    if (W < 1 || H < 1 || W > 32767 || H > 32767) return fail(ctx, OF_E_BADARG, "bad working size");
+    if (u && (uv_step_bytes % 8 || uv_step_bytes < (size_t)W * 8)) return fail(ctx, OF_E_BADARG, "bad uv_step_bytes");
+    if (lp.coeff_bits != 14 && lp.coeff_bits != 15) return fail(ctx, OF_E_BADARG, "coeff_bits must be 14 or 15");
+    if (lp.morph_iterations < 1 || lp.morph_iterations > 4) return fail(ctx, OF_E_BADARG, "morph_iterations must be in 1..4");
+    if (!(lp.learning_rate == lp.learning_rate)) return fail(ctx, OF_E_BADARG, "learning_rate is NaN");
+    int k[31];
+    if (!ofb::build_gauss_kernel_q8(lp.blur_ksize, lp.blur_sigma, k)) return fail(ctx, OF_E_BADARG, "bad blur kernel");
+    const int L = lp.n_levels > 0 ? lp.n_levels : of_get_max_layer(W, H);
+    if (of_status st = check_common(ctx, frame_bgr, frame_bgr, W, H, (size_t)W * 8, L)) return st;
+    OF_CUDA(ctx, cudaSetDevice(ctx->device));
+
+    // device buffers: captured frame, resized frame, two gray frames, two difference images, flow planes
+    const size_t f_pitch = align_up((size_t)width * 3, 256), r_pitch = align_up((size_t)W * 3, 256);
+    const size_t g_pitch = align_up((size_t)W, 256), d_pitch = align_up((size_t)W, 16);          // d_pitch in doubles
+    const size_t b_frame = f_pitch * height, b_res = r_pitch * H, b_gray = g_pitch * H;
+    const size_t b_diff = align_up(d_pitch * H * 8, 256);
+    const size_t need = b_frame + b_res + 2 * b_gray + 4 * b_diff + 256;
+    if (need > ctx->live.cap) ctx->ls = of_ctx::LiveState{};                 // the state lives in the arena
+    if (ctx->ls.w != W || ctx->ls.h != H) ctx->ls = of_ctx::LiveState{};
+    if (of_status st = arena_reserve(ctx, ctx->live, need)) return st;
+    unsigned char* d_frame = (unsigned char*)ctx->live.base;
+    unsigned char* d_res = d_frame + b_frame;
+    unsigned char* d_gray[2] = {d_res + b_res, d_res + b_res + b_gray};
+    double* d_diff[2] = {(double*)(d_res + b_res + 2 * b_gray), (double*)(d_res + b_res + 2 * b_gray + b_diff)};
+    double* d_u = (double*)(d_res + b_res + 2 * b_gray + 2 * b_diff);
+    double* d_v = (double*)(d_res + b_res + 2 * b_gray + 3 * b_diff);
+    of_ctx::LiveState& ls = ctx->ls;
+    ls.w = W;
+    ls.h = H;
+    cudaStream_t s = ctx->stream;
+
+    // :781-791  capture >> frame; resize; GaussianBlur; cvtColor
+    OF_CUDA(ctx, cudaMemcpy2DAsync(d_frame, f_pitch, frame_bgr, step_bytes, (size_t)width * 3, height, cudaMemcpyHostToDevice, s));
+    const unsigned char* blur_src = d_frame;
+    size_t blur_pitch = f_pitch;
+    if (width != W || height != H) {
+        if (of_status st = of_resize_cubic_u8_dev(ctx, d_frame, width, height, f_pitch, 3, d_res, W, H, r_pitch, s)) return st;
+        blur_src = d_res;
+        blur_pitch = r_pitch;
+    }
+    const int g_cur = ls.frames == 0 ? 0 : 1 - ls.cur_gray;
+    OF_CUDA(ctx, ofb::launch_gauss_u8(blur_src, blur_pitch, 3, d_gray[g_cur], g_pitch, W, H, k, lp.blur_ksize, lp.coeff_bits, s,
+                                      &ctx->launches));
+    if (ls.frames == 0) {                                  // :793-797 first frame
+        ls.cur_gray = g_cur;
+        ls.frames = 1;
+        *stage = 0;
+        OF_CUDA(ctx, cudaStreamSynchronize(s));            // the caller may reuse its frame buffer
+        return OF_OK;
+    }
+    // :800-813  diff = cur - 0.3 prev; threshold; Sobel x + y; dilate; erode
+    const int d_cur = ls.frames == 1 ? 0 : 1 - ls.cur_diff;
+    if (of_status st = of_live_diff_f64_dev(ctx, d_gray[g_cur], d_gray[ls.cur_gray], W, H, g_pitch, lp.learning_rate,
+                                            lp.diff_thresh, lp.morph_iterations, d_diff[d_cur], d_pitch * 8, s))
+        return st;
+    ls.cur_gray = g_cur;                                   // prevFrame = current_frame :801
+    if (ls.frames == 1) {                                  // :816-820 first difference image
+        ls.cur_diff = d_cur;
+        ls.frames = 2;
+        *stage = 1;
+        OF_CUDA(ctx, cudaStreamSynchronize(s));
+        return OF_OK;
+    }
+    // :831-832  coarseToFineEstimation(prevDiff, diff, u, v, getMaxLayer(prevDiff)) and :845-888 statistics
+    const size_t st_off = 0;
+    if (of_status st = arena_reserve(ctx, ctx->staging, 256)) return st;
+    of_gesture_stats* d_stats = (of_gesture_stats*)(ctx->staging.base + st_off);
+    of_status st = run_batch(ctx, 1, d_diff[ls.cur_diff], d_diff[d_cur], 0, W, H, d_pitch * 8, L, u ? d_u : nullptr,
+                             u ? d_v : nullptr, 0, d_pitch * 8, nullptr, 0, 0, stats ? d_stats : nullptr, s);
+    if (st) return st;
+    if (!u && !stats) return fail(ctx, OF_E_BADARG, "nothing to compute: stats, u and v are all NULL");
+    if (stats) OF_CUDA(ctx, cudaMemcpyAsync(stats, d_stats, sizeof(of_gesture_stats), cudaMemcpyDeviceToHost, s));
+    if (u) {
+        OF_CUDA(ctx, cudaMemcpy2DAsync(u, uv_step_bytes, d_u, d_pitch * 8, (size_t)W * 8, H, cudaMemcpyDeviceToHost, s));
+        OF_CUDA(ctx, cudaMemcpy2DAsync(v, uv_step_bytes, d_v, d_pitch * 8, (size_t)W * 8, H, cudaMemcpyDeviceToHost, s));
+    }
+    int next_prev = d_cur;
+    if (ctx->params.write_back_warped && L > 1) {
+        // quirk Q1: the reference's diff has been overwritten by its warped version (:700-701) before
+        // prevDiff = diff (:843): frame 2 sampled at -flow / 2 of level 1, into the other slot
+        Plan p = make_plan(W, H, L, 1, false, u == nullptr);
+        ofb::WarpArgs a{};
+        a.cu = (const double*)(ctx->scratch.base + p.flow_u_off[1]);
+        a.cv = (const double*)(ctx->scratch.base + p.flow_v_off[1]);
+        a.c_pitch = p.g[1].pitch;
+        a.wc = p.g[1].w;
+        a.hc = p.g[1].h;
+        a.w = W;
+        a.h = H;
+        a.src = d_diff[d_cur];
+        a.src_pitch = d_pitch;
+        a.dst = d_diff[ls.cur_diff];
+        a.dst_pitch = d_pitch;
+        a.sign = -1.0f;
+        OF_CUDA(ctx, ofb::launch_warp_level(a, s, &ctx->launches));
+        next_prev = ls.cur_diff;
+    }
+    ls.cur_diff = next_prev;                               // prevDiff = diff :843
+    *stage = 2;
+    OF_CUDA(ctx, cudaStreamSynchronize(s));
+    return OF_OK;
+}
+
+}  // extern "C"
+
+extern "C" {
 
 /* ---- host-pointer entry points ------------------------------------------------------- */
 

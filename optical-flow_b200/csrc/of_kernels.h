@@ -127,6 +127,15 @@ cudaError_t launch_gesture_stats(const StatsArgs& a, int n_pairs, cudaStream_t s
 cudaError_t launch_bgr2gray(const unsigned char* bgr, size_t bgr_step, unsigned char* gray, size_t gray_step, int w,
                             int h, int bits, cudaStream_t s, unsigned long long* launches);
 cudaError_t launch_live_diff(const LiveDiffArgs& a, cudaStream_t s, unsigned long long* launches);
+// live-loop colour-frame steps :782, :790 (live_frame.cu).  Tables are host-built and device-resident.
+void build_cubic_table(int src_n, int dst_n, int* ofs, short* co);
+bool build_gauss_kernel_q8(int ksize, double sigma, int* out);
+cudaError_t launch_resize_cubic(const unsigned char* src, size_t sstep, int cn, unsigned char* dst, size_t dstep, int dw,
+                                int dh, const int* xofs, const short* xco, const int* yofs, const float* ybeta,
+                                cudaStream_t s, unsigned long long* launches);
+// gray_bits = 0: blurred image out (cn channels); 14 / 15: cn = 3, cvtColor(BGR2GRAY) fused, one channel out
+cudaError_t launch_gauss_u8(const unsigned char* src, size_t sstep, int cn, unsigned char* dst, size_t dstep, int w, int h,
+                            const int* kernel, int ksize, int gray_bits, cudaStream_t s, unsigned long long* launches);
 // frames of 8-bit pixels (dense planes src_plane bytes apart) -> double planes (dst_plane doubles apart)
 cudaError_t launch_u8_to_f64(const unsigned char* src, size_t src_plane, size_t src_step, double* dst, size_t dst_plane,
                              size_t dst_pitch, int w, int h, int n_frames, double alpha, double beta, cudaStream_t s,

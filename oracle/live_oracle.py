@@ -188,6 +188,8 @@ def resize_cubic_u8(img, dst_w, dst_h):
     return np.clip(np.rint(acc), 0, 255).astype(np.uint8)
 
 
-def live_frame_gray(frame_bgr, size=1080, bits=15):
-    """:782-791: one captured colour frame -> the blurred gray working frame."""
-    return bgr2gray(gaussian_blur_u8(resize_cubic_u8(frame_bgr, size, size)), bits)
+def live_frame_gray(frame_bgr, width=1080, height=1080, bits=15, ksize=9, sigma=1.5):
+    """:782-791: one captured colour frame -> the blurred gray working frame (cv::resize copies when the
+    sizes agree)."""
+    f = frame_bgr if frame_bgr.shape[:2] == (height, width) else resize_cubic_u8(frame_bgr, width, height)
+    return bgr2gray(gaussian_blur_u8(f, ksize, sigma), bits)

@@ -142,3 +142,110 @@ def test_gpu_live_pair_feeds_lk(ofb, c_oracle, live_golden):
     uo, vo, mo = c_oracle.coarse_to_fine(want_prev, want_cur, L, want_mask=True)
     assert np.array_equal(m, mo) and np.array_equal(u, uo) and np.array_equal(v, vo)
     assert (~mo).sum() > 2 * (240 + 160)                     # interior det == 0 pixels exist (sparse input)
+
+
+# ------------------------------------------------------------------ colour-frame steps :782, :790
+@pytest.fixture(scope="module")
+def frame_golden():
+    d = np.load(os.path.join(GOLDEN, "live_frame_golden.npz"))
+    return d["bgr"], d["resized"], d["blurred"], d["gray"]
+
+
+def test_oracle_resize_blur_match_cv2_fixture(frame_golden):
+    """cv2 4.13 (IPP off) wrote the fixture: resize(INTER_CUBIC) 128x96 -> 160x120, GaussianBlur(9x9, 1.5), gray."""
+    bgr, res, blur, gray = frame_golden
+    for k in range(len(bgr)):
+        assert np.array_equal(LO.resize_cubic_u8(bgr[k], 160, 120), res[k])
+        assert np.array_equal(LO.gaussian_blur_u8(res[k]), blur[k])
+        assert np.array_equal(LO.bgr2gray(blur[k], 15), gray[k])
+        assert np.array_equal(LO.live_frame_gray(bgr[k], 160, 120, 15), gray[k])
+    assert tuple(LO.gaussian_kernel_q8(9, 1.5)) == LO.GAUSS9_S15 and sum(LO.GAUSS9_S15) == 256
+
+
+def test_oracle_cubic_table_properties():
+    ofs, co = LO.cubic_table(100, 150)
+    assert (co.sum(axis=1) >= 2046).all() and (co.sum(axis=1) <= 2050).all()      # about 1 in 11-bit fixed point
+    assert ofs.min() == 0 and ofs.max() == 99                                     # taps are clamped to the image
+    ofs, co = LO.cubic_table(64, 64)                                              # same size: identity taps
+    assert (co[:, 1] == 2048).all() and (co[:, [0, 2, 3]] == 0).all()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", [((72, 128, 3), (108, 108)), ((37, 53, 3), (64, 40)), ((120, 200, 1), (50, 70)),
+                                  ((9, 5, 3), (20, 20)), ((160, 240, 3), (1080, 1080)), ((720, 1280, 3), (1080, 1080)),
+                                  ((1080, 1920, 3), (1080, 1080)), ((33, 47, 1), (33, 47))])
+def test_gpu_resize_cubic(ofb, case):
+    import torch
+    shp, (dw, dh) = case
+    rng = np.random.default_rng(shp[0] * 31 + shp[1] + dw)
+    img = rng.integers(0, 256, shp, dtype=np.uint8)
+    src = torch.from_numpy(img if shp[2] == 3 else img[:, :, 0]).cuda()
+    dst = torch.zeros((dh, dw, 3) if shp[2] == 3 else (dh, dw), dtype=torch.uint8, device="cuda")
+    with ofb.Context(0) as ctx:
+        ctx.resize_cubic_dev(src, dst)
+        ctx.synchronize()
+    want = LO.resize_cubic_u8(img, dw, dh) if (dh, dw) != shp[:2] else img
+    assert np.array_equal(dst.cpu().numpy().reshape(dh, dw, shp[2]), want)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("shape", [(1, 1, 3), (3, 2, 3), (9, 5, 3), (37, 53, 3), (64, 257, 1), (160, 240, 3), (1080, 1080, 3)])
+def test_gpu_gaussian_blur(ofb, shape):
+    import torch
+    rng = np.random.default_rng(shape[0] * 13 + shape[1])
+    img = rng.integers(0, 256, shape, dtype=np.uint8)
+    h, w, cn = shape
+    src = torch.from_numpy(img if cn == 3 else img[:, :, 0]).cuda()
+    with ofb.Context(0) as ctx:
+        dst = torch.zeros_like(src)
+        ctx.gaussian_blur_dev(src, dst)
+        ctx.synchronize()
+        want = LO.gaussian_blur_u8(img)
+        assert np.array_equal(dst.cpu().numpy().reshape(shape), want)
+        if cn == 3:
+            for bits in (14, 15):
+                g = torch.zeros((h, w), dtype=torch.uint8, device="cuda")
+                ctx.gaussian_blur_dev(src, g, gray_coeff_bits=bits)
+                ctx.synchronize()
+                assert np.array_equal(g.cpu().numpy(), LO.bgr2gray(want, bits)), bits
+            d5 = torch.zeros_like(src)
+            ctx.gaussian_blur_dev(src, d5, ksize=5, sigma=1.1)
+            ctx.synchronize()
+            assert np.array_equal(d5.cpu().numpy(), LO.gaussian_blur_u8(img, 5, 1.1))
+        with pytest.raises(ofb.OfError):
+            ctx.gaussian_blur_dev(src, dst, ksize=4)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("bits", [14, 15])
+@pytest.mark.parametrize("write_back", [False, True])
+def test_gpu_live_step_matches_the_oracle_chain(ofb, c_oracle, frame_golden, bits, write_back):
+    """of_live_step_u8 over five frames == resize -> blur -> gray -> difference image -> pyramidal LK ->
+    statistics of the oracle, iteration by iteration (main() :769-905); with write_back_warped the next
+    iteration's prevDiff is the warped difference image (quirk Q1, :700-701 + :843)."""
+    from oracle import lk_oracle as O
+    bgr = frame_golden[0]
+    frames = [bgr[0], bgr[1], bgr[2], bgr[1], bgr[0]]
+    W, H = 160, 120
+    L = ofb.getMaxLayer(W, H)
+    gray = [LO.live_frame_gray(f, W, H, bits) for f in frames]
+    with ofb.Context(0, mag_thresh=0.25, count_thresh=20, write_back_warped=write_back) as ctx:
+        prev_diff = None
+        for k, f in enumerate(frames):
+            stage, stats, u, v = ctx.live_step(f, want_flow=True, work_width=W, work_height=H, coeff_bits=bits)
+            assert stage == min(k, 2)
+            if k == 0:
+                continue
+            diff = LO.live_diff(gray[k], gray[k - 1])
+            if k >= 2:
+                tr = {}
+                uo, vo = O.coarse_to_fine(prev_diff, diff, L, trace=tr)
+                assert np.array_equal(u, uo) and np.array_equal(v, vo), "iteration %d" % k
+                s = c_oracle.gesture_stats(uo, vo, 0.25, 20)
+                assert (stats["sum_x"], stats["sum_y"], stats["count"], bool(stats["detected"])) == \
+                    (s["sum_x"], s["sum_y"], s["count"], s["detected"])
+                if write_back:
+                    diff = tr[("B", 0)]                       # the reference's diff is its warped version by now
+            prev_diff = diff
+        ctx.live_reset()
+        assert ctx.live_step(frames[0], work_width=W, work_height=H)[0] == 0
