@@ -122,6 +122,15 @@ def gaussian_kernel_q8(ksize=9, sigma=1.5):
     return out
 
 
+def _r101_any(i, n):
+    """BORDER_REFLECT_101 for any distance (cv::borderInterpolate reflects repeatedly)."""
+    if n == 1:
+        return np.zeros_like(i)
+    p = 2 * (n - 1)
+    i = np.abs(i) % p
+    return np.where(i >= n, p - i, i)
+
+
 def gaussian_blur_u8(img, ksize=9, sigma=1.5):
     """cv::GaussianBlur(img, Size(k, k), sigma, sigma) on 8-bit, any channel count (:790):
     separable, BORDER_REFLECT_101, integer kernel / 256 in both passes, one rounding at the end:
@@ -133,10 +142,10 @@ def gaussian_blur_u8(img, ksize=9, sigma=1.5):
     xs, ys = np.arange(w), np.arange(h)
     row = np.zeros_like(src)
     for d in range(-r, r + 1):
-        row += src[:, _r101(xs + d, w)] * k[d + r]
+        row += src[:, _r101_any(xs + d, w)] * k[d + r]
     col = np.zeros_like(src)
     for d in range(-r, r + 1):
-        col += row[_r101(ys + d, h)] * k[d + r]
+        col += row[_r101_any(ys + d, h)] * k[d + r]
     return np.clip((col + (1 << 15)) >> 16, 0, 255).astype(np.uint8)
 
 
