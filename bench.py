@@ -359,46 +359,49 @@ def run_ours(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_val = world * pairs * e2e_steps / float(t.item())
     frame_bytes = H * W * 8
-    # the same call when only the per-pair gesture statistics come back (what the reference's
-    # live loop consumes, ParallelVideoPyr.cpp:845-905): the read-back shrinks to bytes per pair
-    ctx.flow_stream(fin, LEVELS, want_flow=False)
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(e2e_steps):
-        _, _, stats_h = ctx.flow_stream(fin, LEVELS, want_flow=False)
-    torch.cuda.synchronize()
-    dt = time.perf_counter() - t0
-    t = torch.tensor([dt], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    e2e_stats_val = world * pairs * e2e_steps / float(t.item())
-    stats_bytes = int(stats_h.nbytes)
-    # 8-bit frames in (what imread / VideoCapture deliver; converted on the device like the harness
-    # mains' convertTo(CV_64FC1, 1.0/255)), statistics out: the call the live loop would make.
-    # A longer stream (the 17 frames played forth and back) so that chunks overlap.
-    idx = list(range(pairs + 1)) + list(range(pairs - 1, -1, -1)) + list(range(1, pairs + 1)) + list(range(pairs - 1, -1, -1))
-    q8 = np.clip(np.rint(frames_h * 255.0), 0, 255).astype(np.uint8)[idx]
-    host_q8 = torch.empty(q8.shape, dtype=torch.uint8).pin_memory()
-    host_q8.copy_(torch.from_numpy(q8))
-    f8 = host_q8.numpy()
-    n8 = len(idx) - 1
-    ctx.flow_stream(f8, LEVELS, want_flow=False)
-    barrier()
-    u8_steps = max(2, min(args.steps, 5))
-    t0 = time.perf_counter()
-    for _ in range(u8_steps):
+    e2e_stats_val = e2e_u8_val = None
+    stats_bytes, n8 = 32 * pairs, 0
+    if not args.lean:
+        # the same call when only the per-pair gesture statistics come back (what the reference's
+        # live loop consumes, ParallelVideoPyr.cpp:845-905): the read-back shrinks to bytes per pair
+        ctx.flow_stream(fin, LEVELS, want_flow=False)
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            _, _, stats_h = ctx.flow_stream(fin, LEVELS, want_flow=False)
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        t = torch.tensor([dt], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_stats_val = world * pairs * e2e_steps / float(t.item())
+        stats_bytes = int(stats_h.nbytes)
+        # 8-bit frames in (what imread / VideoCapture deliver; converted on the device like the harness
+        # mains' convertTo(CV_64FC1, 1.0/255)), statistics out: the call the live loop would make.
+        # A longer stream (the 17 frames played forth and back) so that chunks overlap.
+        idx = list(range(pairs + 1)) + list(range(pairs - 1, -1, -1)) + list(range(1, pairs + 1)) + list(range(pairs - 1, -1, -1))
+        q8 = np.clip(np.rint(frames_h * 255.0), 0, 255).astype(np.uint8)[idx]
+        host_q8 = torch.empty(q8.shape, dtype=torch.uint8).pin_memory()
+        host_q8.copy_(torch.from_numpy(q8))
+        f8 = host_q8.numpy()
+        n8 = len(idx) - 1
         ctx.flow_stream(f8, LEVELS, want_flow=False)
-    torch.cuda.synchronize()
-    dt = time.perf_counter() - t0
-    t = torch.tensor([dt], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    e2e_u8_val = world * n8 * u8_steps / float(t.item())
+        barrier()
+        u8_steps = max(2, min(args.steps, 5))
+        t0 = time.perf_counter()
+        for _ in range(u8_steps):
+            ctx.flow_stream(f8, LEVELS, want_flow=False)
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        t = torch.tensor([dt], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_u8_val = world * n8 * u8_steps / float(t.item())
     clocks = sampler.stop()
 
     # ---- the reference's own window (3x3, r = 1; bit-exact path), device-resident like `value` ---
     r1 = None
-    if radius != 1:
+    if radius != 1 and not args.lean:
         with ofb.Context(local_rank, win_radius=1) as c1:
             for _ in range(3):
                 c1.flow_batch_dev(frames, LEVELS, U, V, S)
@@ -508,10 +511,10 @@ def run_ours(args):
             "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": (pairs + 1) * frame_bytes,
                     "d2h_bytes_per_step": 2 * pairs * frame_bytes, "steps": e2e_steps,
                     "api": "of_ctf_f64_stream (pinned host frames in, full u/v flow fields out)"},
-            "e2e_stats_only": {"value": e2e_stats_val, "unit": UNIT, "h2d_bytes_per_step": (pairs + 1) * frame_bytes,
+            "e2e_stats_only": None if args.lean else {"value": e2e_stats_val, "unit": UNIT, "h2d_bytes_per_step": (pairs + 1) * frame_bytes,
                                "d2h_bytes_per_step": stats_bytes,
                                "api": "of_ctf_f64_stream, u = v = NULL: gesture statistics per pair only"},
-            "e2e_u8_stats_only": {"value": e2e_u8_val, "unit": UNIT, "h2d_bytes_per_step": (n8 + 1) * H * W,
+            "e2e_u8_stats_only": None if args.lean else {"value": e2e_u8_val, "unit": UNIT, "h2d_bytes_per_step": (n8 + 1) * H * W,
                                   "d2h_bytes_per_step": 32 * n8, "pairs_per_call": n8,
                                   "api": "of_ctf_u8_stream: 8-bit frames in (the synthetic stream quantised to 8 bits), "
                                          "converted on the device, gesture statistics per pair out"},
@@ -538,7 +541,12 @@ def main():
     ap.add_argument("--pairs", type=int, default=None, help="frame pairs per step per GPU (default: the configuration's)")
     ap.add_argument("--radius", type=int, default=None)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--lean", action="store_true",
+                    help="only the device-resident measurement and the e2e leg (scaling sweeps): no statistics-only, "
+                         "8-bit, 3x3 and CPU legs")
     args = ap.parse_args()
+    if args.lean:
+        args.no_cpu_baseline = True
     global W, H, LEVELS, RADIUS, PAIRS, METRIC, WORKLOAD, REF_PAIRS
     c = CONFIGS[args.config]
     W, H, LEVELS, RADIUS, PAIRS, METRIC, REF_PAIRS = c["w"], c["h"], c["levels"], c["radius"], c["pairs"], c["metric"], c["ref_pairs"]

@@ -21,7 +21,10 @@ namespace ofb {
 
 namespace {
 
-constexpr int PD_NT = 128;      // threads = output columns per CTA
+#ifndef PD_NT_
+#define PD_NT_ 128
+#endif
+constexpr int PD_NT = PD_NT_;      // threads = output columns per CTA
 constexpr int PD_AHEAD = 3;     // output rows whose source loads are in flight
 
 __device__ __forceinline__ int r101_any(int i, int n)
@@ -141,7 +144,10 @@ __global__ void __launch_bounds__(PD_NT) pyr_down_kernel(PyrDownArgs a, int rows
 // only supply their chunk to the neighbour (the chunk is loaded again by the adjacent warp, an L1 /
 // L2 hit), so a row costs one load instruction per warp, a thread keeps 4 registers per row in
 // flight, and 8 CTAs of 128 threads fit an SM with PDF_AHEAD x 2 rows x 16 B in flight per thread.
-constexpr int PDF_AHEAD = 4;
+#ifndef PDF_AHEAD_
+#define PDF_AHEAD_ 4
+#endif
+constexpr int PDF_AHEAD = PDF_AHEAD_;
 constexpr int PDF_WCOLS = 30;                       // output columns per warp
 constexpr int PDF_COLS = PDF_WCOLS * (PD_NT / 32);  // per CTA
 
@@ -164,7 +170,7 @@ __device__ __forceinline__ double pdf_hrow(double2 v, bool first, bool last)
     return dadd(hv, s4);
 }
 
-__global__ void __launch_bounds__(PD_NT, 8) pyr_down_fast_kernel(PyrDownArgs a, int rows_per_cta)
+__global__ void __launch_bounds__(PD_NT, 1024 / PD_NT) pyr_down_fast_kernel(PyrDownArgs a, int rows_per_cta)
 {
     const int img = blockIdx.z;
     const double* __restrict__ src = a.src + (size_t)img * a.src_img_stride;
@@ -229,7 +235,10 @@ cudaError_t launch_pyr_down(const PyrDownArgs& a, cudaStream_t s, unsigned long 
 #ifndef PD_NO_FAST
     if ((a.w & 1) == 0 && a.w >= 4 && (((uintptr_t)a.src | (a.src_pitch * 8) | (a.src_img_stride * 8)) & 15) == 0) {
         const int strips = (ow + PDF_COLS - 1) / PDF_COLS;
-        int rows = 64;
+#ifndef PD_ROWS_
+#define PD_ROWS_ 64
+#endif
+        int rows = PD_ROWS_;
         while (rows > 16 && (long)strips * ((oh + rows - 1) / rows) * a.n_images < (long)current_sm_count() * 16) rows /= 2;
         dim3 grid(strips, (oh + rows - 1) / rows, a.n_images);
         pyr_down_fast_kernel<<<grid, PD_NT, 0, s>>>(a, rows);
