@@ -74,6 +74,17 @@ __device__ unsigned long long g_p1_prof[32 * 8];
 
 namespace {
 
+// The phases of a step are inlined into the step loop.
+// Rare paths (taps outside the image, pyrUp's border columns): inlined.  Out of line (-DPH_OUTLINE_COLD) the step
+// loop shrinks from 47 KB to 33 KB of code, about the size of the 32 KB instruction cache, but the level-0 launch
+// measured 0.965 ms against 0.944 ms: code size is not what bounds the loop.
+#ifdef PH_OUTLINE_COLD
+#define PH_COLD __noinline__
+#else
+#define PH_COLD __forceinline__
+#endif
+#define PH_PHASE __forceinline__        // (as functions of their own, __noinline__: level 0 1.22 ms against 0.94 ms)
+
 constexpr int PH_NT = 512;       // threads per CTA (16 warps; a warp = one row of 32 quads)
 constexpr int PH_NW = PH_NT / 32;
 constexpr int PH_PC = 128;       // product columns per strip = 32 lanes x 4 columns
@@ -185,6 +196,7 @@ __device__ __forceinline__ void up_rows_issue(const CUtensorMap* tmu, const CUte
                                               int k_from, int n_new, double* s_cr, uint64_t* bar)
 {
     mbar_arrive_expect_tx(bar, (uint32_t)n_new * (uint32_t)(2 * CR_W * sizeof(double)));
+#pragma unroll 1
     for (int r = 0; r < n_new; ++r) {
         const int row = pyrup_rho(k_from + r, hc);
         tma_load_3d(s_cr + (2 * r) * CR_PITCH, tmu, j0, row, pair, bar);
@@ -192,10 +204,24 @@ __device__ __forceinline__ void up_rows_issue(const CUtensorMap* tmu, const CUte
     }
 }
 
+// cv::pyrUp's edge formulas for the first / last coarse column (and 0 outside the image), out of line.
+static __device__ PH_COLD void up_border(const double* cu, const double* cv, int j0, int j, int wc, double* d)
+{
+    double eu = 0.0, ou = 0.0, ev = 0.0, ov = 0.0;
+    if ((unsigned)j < (unsigned)wc) {
+        eu = pyrup_row(cu, j0, 2 * j, wc);
+        ou = pyrup_row(cu, j0, 2 * j + 1, wc);
+        ev = pyrup_row(cv, j0, 2 * j, wc);
+        ov = pyrup_row(cv, j0, 2 * j + 1, wc);
+    }
+    *reinterpret_cast<double2*>(d) = make_double2(eu, ev);
+    *reinterpret_cast<double2*>(d + 2) = make_double2(ou, ov);
+}
+
 // Horizontal pass of cv::pyrUp (:646-647) over the landed rows -> HR ring; task = (row, coarse
 // column j) -> fine columns 2j, 2j+1 of both planes.  Fine columns outside the image hold 0.
 template <int NT>
-__device__ __forceinline__ void up_rows_hpass(const PGeo& g, int wc, int k_from, int n_new, const double* s_cr,
+__device__ PH_PHASE void up_rows_hpass(const PGeo& g, int wc, int k_from, int n_new, const double* s_cr,
                                               double* s_hr)
 {
     const int jl = threadIdx.x & 63;
@@ -205,26 +231,23 @@ __device__ __forceinline__ void up_rows_hpass(const PGeo& g, int wc, int k_from,
     for (int r = threadIdx.x >> 6; r < n_new; r += NT / 64) {
         const double* cu = s_cr + (2 * r) * CR_PITCH + jl + 1;       // cu[0] = column j - 1
         const double* cv = cu + CR_PITCH;
-        double eu, ou, ev, ov;
+        double* d = s_hr + ((((k_from + r + 2) & (HR_RING - 1)) * PH_PC) + 2 * jl) * 2;
         if (!border) {
             const double um = cu[0], u0 = cu[1], u1 = cu[2];
             const double vm = cv[0], v0 = cv[1], v1 = cv[2];
-            eu = dadd(dadd(um, dmul(u0, 6.0)), u1);
-            ou = dmul(dadd(u0, u1), 4.0);
-            ev = dadd(dadd(vm, dmul(v0, 6.0)), v1);
-            ov = dmul(dadd(v0, v1), 4.0);
-        } else if ((unsigned)j < (unsigned)wc) {                     // image border: cv::pyrUp's edge formulas
-            eu = pyrup_row(cu - jl - 1, j0, 2 * j, wc);
-            ou = pyrup_row(cu - jl - 1, j0, 2 * j + 1, wc);
-            ev = pyrup_row(cv - jl - 1, j0, 2 * j, wc);
-            ov = pyrup_row(cv - jl - 1, j0, 2 * j + 1, wc);
+            sts2(d, dadd(dadd(um, dmul(u0, 6.0)), u1), dadd(dadd(vm, dmul(v0, 6.0)), v1));
+            sts2(d + 2, dmul(dadd(u0, u1), 4.0), dmul(dadd(v0, v1), 4.0));
         } else {
-            eu = ou = ev = ov = 0.0;
+            up_border(cu - jl - 1, cv - jl - 1, j0, j, wc, d);
         }
-        double* d = s_hr + ((((k_from + r + 2) & (HR_RING - 1)) * PH_PC) + 2 * jl) * 2;
-        sts2(d, eu, ev);
-        sts2(d + 2, ou, ov);
     }
+}
+
+// Rare per-tap path of the remap (a tap outside the image, a non-finite flow).
+static __device__ PH_COLD double remap_tap4_cold(const double* __restrict__ F, size_t pitch, int W, int H, float mx,
+                                                      float my)
+{
+    return remap_tap4(F, pitch, W, H, mx, my);
 }
 
 // ------------------------------------------------------------------------------ P1
@@ -240,7 +263,7 @@ __device__ __forceinline__ void up_rows_hpass(const PGeo& g, int wc, int k_from,
 // (32 x is exact; the only inexact cases are |m| below 2^-120, where both give 0).  A non-finite
 // or huge flow is clamped to 3e38: the tap then lies outside the image like the reference's.
 template <int R>
-__device__ __forceinline__ void phase_remap(const LevelArgs& a, const PGeo& g, const double* __restrict__ A,
+__device__ PH_PHASE void phase_remap(const LevelArgs& a, const PGeo& g, const double* __restrict__ A,
                                             const double* __restrict__ B, double* __restrict__ U,
                                             double* __restrict__ V, int vy0, int r_first, int r_step, int sb,
                                             const double* s_hr, double* s_ab)
@@ -370,7 +393,7 @@ __device__ __forceinline__ void phase_remap(const LevelArgs& a, const PGeo& g, c
                             const float hx = __fmul_rn(hu[i], 1.0f / 32.0f), hy = __fmul_rn(hv[i], 1.0f / 32.0f);
                             const float mx = f ? __fsub_rn(xr, hx) : __fadd_rn(xr, hx);
                             const float my = f ? __fsub_rn(yr, hy) : __fadd_rn(yr, hy);
-                            v[i] = remap_tap4(F, a.img_pitch, W, H, mx, my);
+                            v[i] = remap_tap4_cold(F, a.img_pitch, W, H, mx, my);
                         }
                     }
                 }
@@ -423,7 +446,7 @@ __device__ __forceinline__ void phase_remap(const LevelArgs& a, const PGeo& g, c
                             const float hx = __fmul_rn(hu[i], 1.0f / 32.0f), hy = __fmul_rn(hv[i], 1.0f / 32.0f);
                             const float mx = f ? __fsub_rn(xr, hx) : __fadd_rn(xr, hx);
                             const float my = f ? __fsub_rn(yr, hy) : __fadd_rn(yr, hy);
-                            v[i] = remap_tap4(F, a.img_pitch, W, H, mx, my);
+                            v[i] = remap_tap4_cold(F, a.img_pitch, W, H, mx, my);
                         }
                     }
                 }
@@ -463,7 +486,7 @@ __device__ __forceinline__ void phase_remap(const LevelArgs& a, const PGeo& g, c
 // :44-84), the five products (:383-405) and their horizontal (2R+1)-column window sums in
 // registers + shuffles (additions only).  Rows and columns outside the image contribute 0.
 template <int R>
-__device__ __forceinline__ void phase_products(const PGeo& g, int vy0, int sb, const double* s_ab, double* s_prod)
+__device__ PH_PHASE void phase_products(const PGeo& g, int vy0, int sb, const double* s_ab, double* s_prod)
 {
     using C = PhaseCfg<R>;
     const int W = g.W, H = g.H;
@@ -546,7 +569,7 @@ __device__ __forceinline__ void phase_products(const PGeo& g, int vy0, int sb, c
 // they are read.  Additions only, in the order  row(t+1) + (row(t+2) + ... ).
 // Warp-collective (tcgen05.ld / st): threads without a task run it with active = false.
 template <int R>
-__device__ __forceinline__ void phase_vertical(double* col, uint32_t taddr, bool active)
+__device__ PH_PHASE void phase_vertical(double* col, uint32_t taddr, bool active)
 {
     constexpr int WIN = 2 * R + 1;
     constexpr int ROW = 5 * PhaseCfg<R>::PPITCH;
@@ -672,7 +695,7 @@ __device__ __forceinline__ void solve_pair(const LevelArgs& a, const PGeo& g, do
 // and L + OUT_LANES of the strip's 2 OUT_LANES pairs, so that the lanes' 16-byte accesses to u, v are
 // contiguous; pair p = (quad p / 2, half p % 2) of the pair-split sum rows.
 template <int R, bool VEC>
-__device__ __forceinline__ void phase_solve_row(const LevelArgs& a, const PGeo& g, double* __restrict__ U,
+__device__ PH_PHASE void phase_solve_row(const LevelArgs& a, const PGeo& g, double* __restrict__ U,
                                                 double* __restrict__ V, unsigned char* __restrict__ M, int y,
                                                 const double* s_row, StatAcc& st)
 {
@@ -703,7 +726,7 @@ __device__ __forceinline__ void phase_solve_row(const LevelArgs& a, const PGeo& 
 // ------------------------------------------------------------------------------ R = 1: P2, P4
 // P2 for R = 1: one warp per product row (lane = 4 columns): gradients and the five raw
 // products of all 128 strip columns into the product ring (slot n0 + i).
-__device__ __forceinline__ void phase_products1(const PGeo& g, int vy0, int sb, int n0, const double* s_ab,
+__device__ PH_PHASE void phase_products1(const PGeo& g, int vy0, int sb, int n0, const double* s_ab,
                                                 double* s_prod)
 {
     using C = PhaseCfg<1>;
@@ -779,7 +802,7 @@ __device__ __forceinline__ void phase_products1(const PGeo& g, int vy0, int sb, 
 // L (1 .. 30) the four output columns c0 + 4 L ..; 3x3 sums in get_Sum9's order (:122-157:
 // row-major, starting from 0.0), then the solve of both column pairs.
 template <bool VEC>
-__device__ __forceinline__ void phase_solve1(const LevelArgs& a, const PGeo& g, double* __restrict__ U,
+__device__ PH_PHASE void phase_solve1(const LevelArgs& a, const PGeo& g, double* __restrict__ U,
                                              double* __restrict__ V, unsigned char* __restrict__ M, int y,
                                              int r0, int r1, int r2, const double* s_prod, StatAcc& st)
 {
@@ -872,7 +895,9 @@ __device__ __forceinline__ void stats_flush(const LevelArgs& a, int pair, StatAc
     }
 }
 
-template <int R, bool VEC>
+// HC: the level has a coarser level below it (everything but the coarsest level of a pyramid); a template
+// parameter so that each kernel carries one version of the remap and of the epilogue only (code size).
+template <int R, bool VEC, bool HC>
 __global__ void __launch_bounds__(PH_NT, 1) lk_level_phase_kernel(const __grid_constant__ CUtensorMap tmu,
                                                                   const __grid_constant__ CUtensorMap tmv, LevelArgs a,
                                                                   int th)
@@ -893,7 +918,11 @@ __global__ void __launch_bounds__(PH_NT, 1) lk_level_phase_kernel(const __grid_c
     g.c0 = g.xo0 - 4 * C::HL;
     g.y0 = blockIdx.y * th;
     g.y1 = min(g.y0 + th, a.h);
+#ifdef PH_HC_RUNTIME
     g.has_coarse = a.cu != nullptr;
+#else
+    g.has_coarse = HC;
+#endif
     g.edge = g.c0 < 0 || g.c0 + PH_PC > a.w;
     const int pair = blockIdx.z;
     const int warp = threadIdx.x >> 5;
@@ -1034,7 +1063,7 @@ __global__ void __launch_bounds__(PH_NT, 1) lk_level_phase_kernel(const __grid_c
 //          solve first, so that the latency-bound gathers of one half overlap the FP64 work
 //          of the other.
 // Output row n - 2 (relative to y0) is produced when product row n = s WIN + i has arrived.
-template <bool VEC>
+template <bool VEC, bool HC>
 __global__ void __launch_bounds__(PhaseCfg<1>::NT, PhaseCfg<1>::CTAS)
     lk_level_phase1_kernel(const __grid_constant__ CUtensorMap tmu, const __grid_constant__ CUtensorMap tmv, LevelArgs a,
                            int th)
@@ -1055,7 +1084,11 @@ __global__ void __launch_bounds__(PhaseCfg<1>::NT, PhaseCfg<1>::CTAS)
     g.c0 = g.xo0 - 4 * C::HL;
     g.y0 = blockIdx.y * th;
     g.y1 = min(g.y0 + th, a.h);
+#ifdef PH_HC_RUNTIME
     g.has_coarse = a.cu != nullptr;
+#else
+    g.has_coarse = HC;
+#endif
     g.edge = g.c0 < 0 || g.c0 + PH_PC > a.w;
     const int pair = blockIdx.z;
 
@@ -1122,22 +1155,22 @@ __global__ void __launch_bounds__(PhaseCfg<1>::NT, PhaseCfg<1>::CTAS)
     if (a.stats) stats_flush(a, pair, st);
 }
 
-template <int R, bool VEC>
+template <int R, bool VEC, bool HC>
 cudaError_t launch_phase_v(const LevelArgs& a, int n_pairs, cudaStream_t s, unsigned long long* launches)
 {
     using C = PhaseCfg<R>;
     static SmemOptIn opt_in;
     {
         cudaError_t e;
-        if constexpr (R == 1) e = opt_in.ensure((const void*)lk_level_phase1_kernel<VEC>, C::SMEM_BYTES);
-        else e = opt_in.ensure((const void*)lk_level_phase_kernel<R, VEC>, C::SMEM_BYTES);
+        if constexpr (R == 1) e = opt_in.ensure((const void*)lk_level_phase1_kernel<VEC, HC>, C::SMEM_BYTES);
+        else e = opt_in.ensure((const void*)lk_level_phase_kernel<R, VEC, HC>, C::SMEM_BYTES);
         if (e != cudaSuccess) return e;
     }
     // tensor maps of the coarse flow planes (x, y, pair), one box = CR_W columns of one row
     CUtensorMap tmu, tmv;
     memset(&tmu, 0, sizeof tmu);
     memset(&tmv, 0, sizeof tmv);
-    if (a.cu) {
+    if constexpr (HC) {
         cudaError_t e = tma_map_planes_f64(&tmu, a.cu, a.wc, a.hc, a.c_pitch, a.c_pair_stride, n_pairs, CR_W, 1);
         if (e == cudaSuccess) e = tma_map_planes_f64(&tmv, a.cv, a.wc, a.hc, a.c_pitch, a.c_pair_stride, n_pairs, CR_W, 1);
         if (e != cudaSuccess) return e;
@@ -1162,8 +1195,8 @@ cudaError_t launch_phase_v(const LevelArgs& a, int n_pairs, cudaStream_t s, unsi
     }
     const int chunks = (a.h + th - 1) / th;
     dim3 grid(strips, chunks, n_pairs);
-    if constexpr (R == 1) lk_level_phase1_kernel<VEC><<<grid, C::NT, C::SMEM_BYTES, s>>>(tmu, tmv, a, th);
-    else lk_level_phase_kernel<R, VEC><<<grid, C::NT, C::SMEM_BYTES, s>>>(tmu, tmv, a, th);
+    if constexpr (R == 1) lk_level_phase1_kernel<VEC, HC><<<grid, C::NT, C::SMEM_BYTES, s>>>(tmu, tmv, a, th);
+    else lk_level_phase_kernel<R, VEC, HC><<<grid, C::NT, C::SMEM_BYTES, s>>>(tmu, tmv, a, th);
     if (launches) *launches += 1;
     return cudaGetLastError();
 }
@@ -1175,7 +1208,8 @@ cudaError_t launch_phase(const LevelArgs& a, int n_pairs, cudaStream_t s, unsign
 {
     const bool vec = ((reinterpret_cast<uintptr_t>(a.u) | reinterpret_cast<uintptr_t>(a.v) | (a.uv_pitch * 8) |
                        (n_pairs > 1 ? a.uv_pair_stride * 8 : 0)) & 15) == 0;
-    return vec ? launch_phase_v<R, true>(a, n_pairs, s, launches) : launch_phase_v<R, false>(a, n_pairs, s, launches);
+    if (a.cu) return vec ? launch_phase_v<R, true, true>(a, n_pairs, s, launches) : launch_phase_v<R, false, true>(a, n_pairs, s, launches);
+    return vec ? launch_phase_v<R, true, false>(a, n_pairs, s, launches) : launch_phase_v<R, false, false>(a, n_pairs, s, launches);
 }
 
 }  // namespace
