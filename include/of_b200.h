@@ -294,6 +294,24 @@ OF_API of_status of_mgpu_ctf_u8_stream(of_mgpu *m, const unsigned char *frames, 
                                 double *u, double *v, size_t uv_pair_stride_bytes,
                                 size_t uv_step_bytes, of_gesture_stats *stats);
 
+/* ---- allocation-free variant (no counterpart in the reference)
+ * ------------------------------------------------------------------------------------------
+ * of_ctf_f64_dev for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid it): the same kernels and results for ONE pair, with the device scratch
+ * (pyramid levels >= 1 of both frames, flows of the levels >= 1; about 10.7 bytes per level-0 pixel) in a
+ * static device array of OF_STATIC_SCRATCH_BYTES inside the library instead of the context's arena.  The
+ * call allocates nothing (no cudaMalloc / cudaFree / allocating library routine); every GPU that loads
+ * the library holds the array until the process exits.  Sizes that need more scratch are rejected with
+ * OF_E_BADARG and a message naming both numbers (32 MiB covers up to 1920x1080 at any depth).  The array
+ * is shared by every call on a device and keeps the last call's contents; nothing in it has to start at
+ * zero.  Calls that overlap on one GPU race on it: serialise them (one stream, or events between them).
+ * All pointers are device pointers; stream as in of_ctf_f64_dev; no mask, no statistics; rejects
+ * write_back_warped like the other _dev calls. */
+#define OF_STATIC_SCRATCH_BYTES (32u << 20)
+OF_API of_status of_ctf_f64_dev_static(of_ctx *ctx, const double *img1, const double *img2,
+                                int width, int height, size_t step_bytes, int n_levels,
+                                double *u, double *v, size_t uv_step_bytes, void *stream);
+
 /* Number of kernel launches issued through this context since creation (bench evidence). */
 OF_API unsigned long long of_ctx_launch_count(const of_ctx *ctx);
 

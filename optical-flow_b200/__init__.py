@@ -30,7 +30,7 @@ EXPORTS = (
     "of_ctf_f64_batch_dev", "of_gesture_stats_dev", "of_pyr_down_f64_dev",
     "of_ctx_synchronize", "of_ctx_launch_count", "of_ctx_set_timing", "of_ctx_get_timing",
     "of_bgr2gray_u8_dev", "of_live_diff_f64_dev", "of_live_diff_f64", "of_ctf_u8_stream",
-    "of_ctx_get_level_f64", "of_ctx_graph_replay_count",
+    "of_ctx_get_level_f64", "of_ctx_graph_replay_count", "of_ctf_f64_dev_static",
     "of_resize_cubic_u8_dev", "of_gaussian_blur_u8_dev", "of_live_params_default", "of_live_step_u8", "of_live_reset",
     "of_mgpu_create", "of_mgpu_destroy", "of_mgpu_device_count", "of_mgpu_context", "of_mgpu_last_error_string",
     "of_mgpu_partition", "of_mgpu_ctf_f64_stream", "of_mgpu_ctf_u8_stream",
@@ -100,6 +100,7 @@ def lib():
     L.of_ctf_u8_stream.argtypes = [vp, vp, ci, sz, ci, ci, sz, dbl, dbl, ci, vp, vp, sz, sz, vp]
     L.of_lk_single_f64_dev.argtypes = [vp, vp, vp, ci, ci, sz, vp, vp, sz, vp, sz, vp]
     L.of_ctf_f64_dev.argtypes = [vp, vp, vp, ci, ci, sz, ci, vp, vp, sz, vp, sz, vp]
+    L.of_ctf_f64_dev_static.argtypes = [vp, vp, vp, ci, ci, sz, ci, vp, vp, sz, vp]
     L.of_ctf_f64_batch_dev.argtypes = [vp, ci, vp, vp, sz, ci, ci, sz, ci, vp, vp, sz, sz,
                                        vp, sz, sz, vp, vp]
     L.of_gesture_stats_dev.argtypes = [vp, ci, vp, vp, sz, ci, ci, sz, vp, vp]

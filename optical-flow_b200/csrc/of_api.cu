@@ -1351,3 +1351,141 @@ of_status of_ctf_u8_stream(of_ctx* ctx, const unsigned char* frames, int n_frame
 }
 
 }  // extern "C"
+
+/* ---- allocation-free variant: scratch in a static device array -------------------------------------
+ * No counterpart in the reference; added for callers that cannot
+ * call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * of_ctf_f64_dev_static is of_ctf_f64_dev for one pair with the pyramid levels >= 1 of both frames and
+ * the accumulated flows of the levels >= 1 (what run_batch keeps in the context's cudaMalloc'ed arena)
+ * in the file-scope array below.  Same kernels, same launch sequence, same results.
+ *
+ * The array belongs to the library, not to a context: every GPU that loads the library holds its
+ * OF_STATIC_SCRATCH_BYTES until the process exits, every call on a device shares it, and it keeps the
+ * last call's contents.  Nothing in it has to start at zero (every plane is written in full by the call
+ * before the call reads it), so nothing is cleared.  Calls that overlap on one GPU (different streams,
+ * different contexts, different threads) race on it; serialise them.
+ */
+static __device__ __align__(256) unsigned char g_static_scratch[OF_STATIC_SCRATCH_BYTES];
+
+namespace {
+
+// In host code `g_static_scratch` is a host-side stand-in for the symbol, not a device address: the
+// address comes from cudaGetSymbolAddress, once per device, with that device current.
+of_status static_scratch_address(of_ctx* ctx, char** out)
+{
+    static std::atomic<char*> cache[64];
+    int dev = 0;
+    OF_CUDA(ctx, cudaGetDevice(&dev));
+    if (dev >= 0 && dev < 64) {
+        if (char* p = cache[dev].load(std::memory_order_acquire)) {
+            *out = p;
+            return OF_OK;
+        }
+    }
+    void* p = nullptr;
+    OF_CUDA(ctx, cudaGetSymbolAddress(&p, g_static_scratch));
+    if (!p) return fail(ctx, OF_E_CUDA, "cudaGetSymbolAddress returned a null address for the static scratch");
+    if (dev >= 0 && dev < 64) cache[dev].store((char*)p, std::memory_order_release);
+    *out = (char*)p;
+    return OF_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+of_status of_ctf_f64_dev_static(of_ctx* ctx, const double* img1, const double* img2, int width, int height,
+                                size_t step_bytes, int n_levels, double* u, double* v, size_t uv_step_bytes,
+                                void* stream)
+{
+    of_status st = check_common(ctx, img1, img2, width, height, step_bytes, n_levels);
+    if (st) return st;
+    if (!u || !v) return fail(ctx, OF_E_BADARG, "null flow pointer");
+    if (uv_step_bytes % sizeof(double) || uv_step_bytes < (size_t)width * sizeof(double))
+        return fail(ctx, OF_E_BADARG, "uv_step_bytes %zu invalid for width %d", uv_step_bytes, width);
+    if ((st = reject_write_back(ctx, n_levels, "of_ctf_f64_dev_static"))) return st;
+    const Plan p = make_plan(width, height, n_levels, 1, false, false);
+    if (p.total > (size_t)OF_STATIC_SCRATCH_BYTES)
+        return fail(ctx, OF_E_BADARG,
+                    "of_ctf_f64_dev_static: %dx%d with %d levels needs %zu bytes of scratch, the static array holds %zu "
+                    "(OF_STATIC_SCRATCH_BYTES); use of_ctf_f64_dev",
+                    width, height, n_levels, p.total, (size_t)OF_STATIC_SCRATCH_BYTES);
+    OF_CUDA(ctx, cudaSetDevice(ctx->device));
+    char* base = nullptr;
+    if ((st = static_scratch_address(ctx, &base))) return st;
+    cudaStream_t s = pick(ctx, stream);
+    const size_t in_pitch = step_bytes / sizeof(double);
+    const int L = n_levels;
+
+    // Gaussian pyramids (getGaussianPyramid :566-575): frame 1 in image slot 0, frame 2 in slot 1 of every level
+    for (int l = 1; l < L; ++l) {
+        const LevelGeom& gs = p.g[l - 1];
+        const LevelGeom& gd = p.g[l];
+        ofb::PyrDownArgs a{};
+        a.w = gs.w;
+        a.h = gs.h;
+        a.dst = (double*)(base + p.pyr_off[l]);
+        a.dst_pitch = gd.pitch;
+        a.dst_img_stride = gd.img_stride;
+        if (l == 1) {
+            a.src_pitch = in_pitch;
+            a.n_images = 1;
+            a.src = img1;
+            OF_CUDA(ctx, ofb::launch_pyr_down(a, s, &ctx->launches));
+            a.src = img2;
+            a.dst += gd.img_stride;
+            OF_CUDA(ctx, ofb::launch_pyr_down(a, s, &ctx->launches));
+        } else {
+            a.src = (const double*)(base + p.pyr_off[l - 1]);
+            a.src_pitch = gs.pitch;
+            a.src_img_stride = gs.img_stride;
+            a.n_images = 2;
+            OF_CUDA(ctx, ofb::launch_pyr_down(a, s, &ctx->launches));
+        }
+    }
+    // coarse to fine (:610-703), one fused launch per level
+    for (int l = L - 1; l >= 0; --l) {
+        const LevelGeom& g = p.g[l];
+        ofb::LevelArgs a{};
+        a.w = g.w;
+        a.h = g.h;
+        a.radius = ctx->params.win_radius;
+        a.det_eps = ctx->params.det_eps;
+        a.mag_thresh = ctx->params.mag_thresh;
+        a.mag2_thresh = mag2_threshold(ctx->params.mag_thresh);
+        if (l == 0) {
+            a.A = img1;
+            a.B = img2;
+            a.img_pitch = in_pitch;
+        } else {
+            const double* pyr = (const double*)(base + p.pyr_off[l]);
+            a.A = pyr;
+            a.B = pyr + g.img_stride;
+            a.img_pitch = g.pitch;
+            a.a_pair_stride = a.b_pair_stride = g.img_stride;
+        }
+        if (l < L - 1) {
+            const LevelGeom& gc = p.g[l + 1];
+            a.cu = (const double*)(base + p.flow_u_off[l + 1]);
+            a.cv = (const double*)(base + p.flow_v_off[l + 1]);
+            a.c_pitch = gc.pitch;
+            a.c_pair_stride = gc.img_stride;
+            a.wc = gc.w;
+            a.hc = gc.h;
+        }
+        if (l == 0) {
+            a.u = u;
+            a.v = v;
+            a.uv_pitch = uv_step_bytes / sizeof(double);
+        } else {
+            a.u = (double*)(base + p.flow_u_off[l]);
+            a.v = (double*)(base + p.flow_v_off[l]);
+            a.uv_pitch = g.pitch;
+            a.uv_pair_stride = g.img_stride;
+        }
+        OF_CUDA(ctx, launch_lk_level(ctx, a, 1, s));
+    }
+    return OF_OK;
+}
+
+}  // extern "C"
