@@ -81,6 +81,18 @@ def measured_peaks():
     return 6650.0, "fallback"
 
 
+def config_block(args, world):
+    """The `config` object of the JSON line: the workload BASELINE.json names -- identical in both arms (ours and
+    --impl reference); how much of it an arm's step covers is said in that arm's own fields (the reference arm's
+    bounded sample: cpu_baseline.sample)."""
+    frame_bytes = H * W * 8
+    return {"workload": WORKLOAD, "name": args.config, "width": W, "height": H, "levels": LEVELS,
+            "win_radius": args.radius, "pairs_per_step": args.pairs,
+            "l2": "inputs+outputs per step (%.0f MB) exceed the 126 MB L2; no flush" %
+                  (((args.pairs + 1) + 2 * args.pairs) * frame_bytes / 1e6),
+            "exchange": "per-step gather of gesture statistics (32 B/pair) to rank 0" if world > 1 else "none"}
+
+
 def recorded(name):
     """A committed measurement under profiles/ (ncu-derived constants the live run cannot take itself)."""
     try:
@@ -236,8 +248,7 @@ def run_reference(args):
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
         "data": "synthetic",
-        "config": {"workload": WORKLOAD, "width": W, "height": H, "levels": LEVELS, "win_radius": radius,
-                   "pairs_per_step": sample},
+        "config": config_block(args, args.gpus),
         "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port",
                          "sample": "%d steps x %d consecutive pairs of the same synthetic stream, "
                                    "oracle/lk_oracle.c (gcc -O3 -fopenmp), all host threads" % (args.steps, sample)},
@@ -503,11 +514,7 @@ def run_ours(args):
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "timed": {"repetitions": n_reps, "steps_per_repetition": args.steps, "reported": "median repetition",
                       "rep_ms_min": min(rep_ms), "rep_ms_max": max(rep_ms), "min_timed_s": MIN_TIMED_S},
-            "config": {"workload": WORKLOAD, "name": args.config,
-                       "width": W, "height": H, "levels": LEVELS, "win_radius": radius, "pairs_per_step": pairs,
-                       "l2": "inputs+outputs per step (%.0f MB) exceed the 126 MB L2; no flush" %
-                             (((pairs + 1) + 2 * pairs) * frame_bytes / 1e6),
-                       "exchange": "per-step gather of gesture statistics (32 B/pair) to rank 0" if world > 1 else "none"},
+            "config": config_block(args, world),
             "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": (pairs + 1) * frame_bytes,
                     "d2h_bytes_per_step": 2 * pairs * frame_bytes, "steps": e2e_steps,
                     "api": "of_ctf_f64_stream (pinned host frames in, full u/v flow fields out)"},

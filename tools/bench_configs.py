@@ -116,6 +116,9 @@ def main():
     f = synth.synth_frames(17, 1080, 1920, seed=1234)
     out.append(run("synthetic 1080p, 15x15 (configs[3])", f, 3, 7, "stream", 4, 20))
     out.append(run("synthetic 1080p, 3x3 (configs[3], the reference's window)", f, 3, 1, "stream", 4, 20))
+    f = synth.synth_frames(17, 1080, 1920, seed=1234, gesture=True)
+    out.append(run("synthetic 1080p gesture-like stream (moving disc, exact zeros elsewhere), 15x15", f, 3, 7, "stream", 4, 20))
+    out.append(run("synthetic 1080p gesture-like stream, 3x3", f, 3, 1, "stream", 4, 20))
     f = synth.synth_frames(17, 1080, 1080, seed=1234)
     out.append(run("synthetic 1080x1080 L=4 3x3 (the live loop's size, ParallelVideoPyr.cpp:782)", f, 4, 1, "stream", 4, 20))
     f = synth.synth_frames(9, 2160, 3840, seed=1234)
