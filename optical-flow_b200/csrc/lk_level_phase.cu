@@ -121,12 +121,12 @@ struct PhaseCfg {
     static constexpr int O_AB = al16(PROD_D);
     static constexpr int O_HR = O_AB + al16(AB_D);
     static constexpr int O_CR = O_HR + HR_D;
-    static constexpr int O_BAR = O_CR + CR_D;              // mbarrier (8 bytes) + TMEM base address (4 bytes)
+    static constexpr int O_BAR = O_CR + CR_D;              // mbarrier (8 bytes), TMEM base address (4 bytes), P3 mbarrier
     // Tensor memory: a P3 thread keeps the 2R raw rows 1 .. 2R of the previous vertical block of its
     // (channel, column pair) there, 2R x 2 doubles = 8R columns; a column slot of 64 per warp
     static constexpr int TM_SLOT = 64;
     static constexpr int TM_COLS = 256;
-    static constexpr size_t SMEM_BYTES = (size_t)(O_BAR + 2) * 8;
+    static constexpr size_t SMEM_BYTES = (size_t)(O_BAR + 3) * 8;
     static constexpr int VPAIRS = 2 * OUT_LANES;      // column pairs per channel in P3
     static constexpr int NT = PH_NT;
 };
@@ -913,6 +913,7 @@ __global__ void __launch_bounds__(PH_NT, 1) lk_level_phase_kernel(const __grid_c
     double* s_cr = sm + C::O_CR;
     uint64_t* s_bar = reinterpret_cast<uint64_t*>(sm + C::O_BAR);
     uint32_t* s_tmem = reinterpret_cast<uint32_t*>(sm + C::O_BAR + 1);
+    uint64_t* s_p3bar = reinterpret_cast<uint64_t*>(sm + C::O_BAR + 2);
 
     PGeo g;
     g.W = a.w;
@@ -948,6 +949,7 @@ __global__ void __launch_bounds__(PH_NT, 1) lk_level_phase_kernel(const __grid_c
     }
     if (threadIdx.x == 0) {
         mbar_init(s_bar, 1);
+        mbar_init(s_p3bar, V_WARPS);                     // one arrival per V warp and step
         mbar_fence_init();
     }
     if (warp == 0) tmem_alloc(s_tmem, C::TM_COLS);
@@ -970,11 +972,10 @@ __global__ void __launch_bounds__(PH_NT, 1) lk_level_phase_kernel(const __grid_c
     // Schedule of a step (two block-wide barriers):
     //   beta : thread 0 hands the coarse rows of step s+1 to the copy engine; P2(s); then the horizontal
     //          pyrUp pass over the landed rows
-    //   gamma: the first V_WARPS warps ("V") run P3(s) and signal barrier 1; every warp then warps
-    //          its row of P1(s+1); finally P4(s) row by row in the warps that have time for it: the
-    //          other warps ("O"), which wait on barrier 1 first, and the V warps without a P1 row.
-    //          The latency-bound gathers thus overlap the shared-memory-bound vertical sums and
-    //          the arithmetic of the solve.
+    //   gamma: the first V_WARPS warps ("V") run P3(s) and arrive on a shared-memory barrier; every warp
+    //          then warps its row of P1(s+1); finally every warp waits for that barrier (P3 done in all
+    //          V warps) and solves its row of P4(s).  The latency-bound gathers thus overlap the
+    //          shared-memory-bound vertical sums and the arithmetic of the solve.
     // The loop starts at s = -1 (only P0(0), P1(0)) so that every phase has a single call site:
     // the code of a step has to stay small enough for the instruction cache.
     constexpr int O_WARPS = PH_NW - V_WARPS;
@@ -996,6 +997,7 @@ __global__ void __launch_bounds__(PH_NT, 1) lk_level_phase_kernel(const __grid_c
     cur.any = false;
     int k_have = -1000;                                // highest coarse row in the ring
     unsigned up_par = 0;                               // phase parity of the landing-buffer barrier
+    unsigned p3_par = 0;                               // ... and of the P3 barrier
 #ifdef PH_PROF
     long long prof_acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     long long prof_t = clock64();
@@ -1026,8 +1028,15 @@ __global__ void __launch_bounds__(PH_NT, 1) lk_level_phase_kernel(const __grid_c
 #ifndef PH_KNOCK_P3
             phase_vertical<R>(s_prod + voff, tm_mine, v_task);
 #endif
+#ifdef PH_NAMED_BARRIERS
             asm volatile("bar.arrive 1, %0;" ::"n"(PH_NT) : "memory");
             asm volatile("bar.sync 2, %0;" ::"n"(V_WARPS * 32) : "memory");   // P3 done in all V warps
+#else
+            // "my part of P3 is done": an arrival on a shared-memory barrier, which nobody waits for before P4,
+            // so that a V warp goes on to its P1 row at once instead of waiting for the slowest V warp here
+            __syncwarp();
+            if ((threadIdx.x & 31) == 0) mbar_arrive(s_p3bar);
+#endif
         }
         PH_MARK(2);
         {
@@ -1036,7 +1045,12 @@ __global__ void __launch_bounds__(PH_NT, 1) lk_level_phase_kernel(const __grid_c
         }
         PH_MARK(3);
         if (s >= 0) {
+#ifdef PH_NAMED_BARRIERS
             if (warp >= V_WARPS) asm volatile("bar.sync 1, %0;" ::"n"(PH_NT) : "memory");
+#else
+            if (p4_idx >= 0) mbar_wait(s_p3bar, p3_par);     // P3 done in all V warps
+            p3_par ^= 1u;
+#endif
             PH_MARK(4);
 #ifndef PH_KNOCK_P4
             if (p4_idx >= 0)
