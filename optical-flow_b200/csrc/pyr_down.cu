@@ -235,11 +235,17 @@ cudaError_t launch_pyr_down(const PyrDownArgs& a, cudaStream_t s, unsigned long 
 #ifndef PD_NO_FAST
     if ((a.w & 1) == 0 && a.w >= 4 && (((uintptr_t)a.src | (a.src_pitch * 8) | (a.src_img_stride * 8)) & 15) == 0) {
         const int strips = (ow + PDF_COLS - 1) / PDF_COLS;
-#ifndef PD_ROWS_
-#define PD_ROWS_ 64
-#endif
-        int rows = PD_ROWS_;
-        while (rows > 16 && (long)strips * ((oh + rows - 1) / rows) * a.n_images < (long)current_sm_count() * 16) rows /= 2;
+        // Output rows per CTA: the height that minimises (waves of resident CTAs) x (rows + the ~6 row-times a CTA
+        // spends on its three warm-up source rows and on filling its load pipeline).  A fixed 64 rows put the 1080p
+        // batch at 1224 CTAs against 1184 resident ones -- two waves, the second one nearly empty.
+        const long slots = (long)current_sm_count() * (1024 / PD_NT);
+        int rows = 64;
+        long best = -1;
+        for (int r = 8; r <= 128; r += PDF_AHEAD) {
+            const long ctas = (long)strips * ((oh + r - 1) / r) * a.n_images;
+            const long cost = ((ctas + slots - 1) / slots) * (r + 6);
+            if (best < 0 || cost <= best) { best = cost; rows = r; }
+        }
         dim3 grid(strips, (oh + rows - 1) / rows, a.n_images);
         pyr_down_fast_kernel<<<grid, PD_NT, 0, s>>>(a, rows);
         if (launches) *launches += 1;
