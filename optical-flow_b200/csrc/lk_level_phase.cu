@@ -74,19 +74,15 @@ __device__ unsigned long long g_p1_prof[32 * 8];
 
 namespace {
 
-// The phases of a step are inlined into the step loop.
-// Rare paths (taps outside the image, pyrUp's border columns): inlined.  Out of line (-DPH_OUTLINE_COLD) the step
-// loop shrinks from 47 KB to 33 KB of code, about the size of the 32 KB instruction cache, but the level-0 launch
-// measured 0.965 ms against 0.944 ms: code size is not what bounds the loop.
-#ifdef PH_OUTLINE_COLD
-#define PH_COLD __noinline__
-#else
+// The phases of a step and their rare paths (taps outside the image, pyrUp's border columns) are inlined into the
+// step loop.  Measured alternatives: every phase a function of its own 1.22 ms per level-0 launch
+// against 0.94; the rare paths out of line (step loop 47 KB -> 33 KB of code, about the size of the instruction
+// cache) 0.965 against 0.944 -- code size is not what bounds the loop; for R >= 2 a blend written as three
+// interpolations (two exact fractions instead of four weights, ~12 integer instructions per pixel less) 0.909
+// against 0.920, but it moves the noise that ill-conditioned coarse pixels hand down outside the validity mask from
+// 2e-3 to 1.3e-2 px at 4K and was not taken.
 #define PH_COLD __forceinline__
-#endif
-// (R >= 2: a blend written as three interpolations with two exact fractions instead of four weights saves
-// ~12 integer instructions per pixel -- level 0 0.920 -> 0.909 ms -- but moves the noise that ill-conditioned
-// coarse pixels hand down outside the validity mask from 2e-3 to 1.3e-2 px at 4K; not taken.)
-#define PH_PHASE __forceinline__        // (as functions of their own, __noinline__: level 0 1.22 ms against 0.94 ms)
+#define PH_PHASE __forceinline__
 
 constexpr int PH_NT = 512;       // threads per CTA (16 warps; a warp = one row of 32 quads)
 constexpr int PH_NW = PH_NT / 32;
@@ -319,11 +315,7 @@ __device__ PH_PHASE void phase_remap(const LevelArgs& a, const PGeo& g, const do
             }
             P1_MARK(1);
             // park the upsampled flow of output pixels for the epilogue (tmpu += upu, :634-637)
-#ifdef PH_KNOCK_PARK
-            if (false) {
-#else
             if (vy == yy && vy >= g.y0 && vy < g.y1) {
-#endif
                 const int off = vy * (int)a.uv_pitch + x0;
                 double* pu = U + off;
                 double* pv = V + off;
@@ -348,7 +340,6 @@ __device__ PH_PHASE void phase_remap(const LevelArgs& a, const PGeo& g, const do
             }
             const float xf = (float)(32 * x0), yf = (float)(32 * yy);
             // frame 1 is sampled at (x + f.x / 2, y + f.y / 2), frame 2 at (x - f.x / 2, y - f.y / 2)
-#ifndef PH_P1_SEQ
             // both frames' 32 gathers in flight before the first blend (measured: level 0 0.976 -> 0.910 ms)
             int off[2][4], fr[2][4];
             unsigned out = 0;
@@ -401,60 +392,6 @@ __device__ PH_PHASE void phase_remap(const LevelArgs& a, const PGeo& g, const do
                     }
                 }
             }
-#else
-#pragma unroll
-            for (int f = 0; f < 2; ++f) {
-                const double* __restrict__ F = f ? B : A;
-                int off[4], ax[4], ay[4];
-                unsigned out = 0;                            // taps not inside the image
-#pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    const float xi = __fadd_rn(xf, 1024.0f * (float)i);
-                    const int sx = __float2int_rn(f ? __fsub_rn(xi, hu[i]) : __fadd_rn(xi, hu[i]));
-                    const int sy = __float2int_rn(f ? __fsub_rn(yf, hv[i]) : __fadd_rn(yf, hv[i]));
-                    const int ix = sx >> 5, iy = sy >> 5;
-                    const bool interior = (unsigned)ix < (unsigned)(W - 1) && (unsigned)iy < (unsigned)(H - 1);
-                    off[i] = interior ? iy * pitch + ix : 0;
-                    if (!interior) out |= 1u << i;
-                    ax[i] = sx & 31;
-                    ay[i] = sy & 31;
-                }
-                double sv[4][4];                             // 16 gathers, issued back to back
-#pragma unroll
-                for (int i = 0; i < 4; ++i) {
-#ifdef PH_KNOCK_L1
-                    const double* pa = F + ((unsigned)off[i] & 1023u);
-#else
-                    const double* pa = F + (unsigned)off[i];
-#endif
-                    sv[i][0] = __ldg(pa); sv[i][1] = __ldg(pa + 1);
-                    sv[i][2] = __ldg(pa + pitch); sv[i][3] = __ldg(pa + pitch + 1);
-                }
-                double* v = f ? vb : va;
-                P1_MARK(3 + 2 * f);
-#pragma unroll
-                for (int i = 0; i < 4; ++i)
-#ifdef PH_KNOCK_BLEND
-                    v[i] = dadd(dadd(sv[i][0], sv[i][1]), dadd(sv[i][2], __hiloint2double(sv[i][3] > 0.5 ? ax[i] : ay[i], 0)));
-#else
-                    v[i] = R == 1 ? blend4_exact(sv[i][0], sv[i][1], sv[i][2], sv[i][3], ax[i], ay[i])
-                                  : blend4(sv[i][0], sv[i][1], sv[i][2], sv[i][3], ax[i], ay[i]);
-#endif
-                P1_MARK(4 + 2 * f);
-                if (out) {                                   // rare: a tap outside the image, non-finite flow
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) {
-                        if (((out >> i) & 1u) && (unsigned)(x0 + 32 * i) < (unsigned)W) {
-                            const float xr = (float)(x0 + 32 * i), yr = (float)yy;
-                            const float hx = __fmul_rn(hu[i], 1.0f / 32.0f), hy = __fmul_rn(hv[i], 1.0f / 32.0f);
-                            const float mx = f ? __fsub_rn(xr, hx) : __fadd_rn(xr, hx);
-                            const float my = f ? __fsub_rn(yr, hy) : __fadd_rn(yr, hy);
-                            v[i] = remap_tap4_cold(F, a.img_pitch, W, H, mx, my);
-                        }
-                    }
-                }
-            }
-#endif
         } else {
             const double* pa = A + (size_t)yy * a.img_pitch + x0;
             const double* pb = B + (size_t)yy * a.img_pitch + x0;
@@ -653,18 +590,8 @@ __device__ __forceinline__ void solve_pair(const LevelArgs& a, const PGeo& g, do
         fast = (div2_fast(nus[q], nvs[q], dets[q], lu[q], lv[q]) || !ok) && fast;
     }
     if (!fast) {                                         // rare: exponent range outside the fast path
-#ifdef PH_DIV_PER_QUOTIENT
-#pragma unroll
-        for (int q = 0; q < 2; ++q) {
-            if ((okbits >> q) & 1u) {
-                lu[q] = ddiv_slow(nus[q], dets[q]);
-                lv[q] = ddiv_slow(nvs[q], dets[q]);
-            }
-        }
-#else
         const Quot4 q4 = div4_slow(nus[0], nvs[0], dets[0], nus[1], nvs[1], dets[1]);
         lu[0] = q4.u0; lv[0] = q4.v0; lu[1] = q4.u1; lv[1] = q4.v1;
-#endif
     }
     double fu[2], fv[2];
 #pragma unroll
@@ -922,11 +849,7 @@ __global__ void __launch_bounds__(PH_NT, 1) lk_level_phase_kernel(const __grid_c
     g.c0 = g.xo0 - 4 * C::HL;
     g.y0 = blockIdx.y * th;
     g.y1 = min(g.y0 + th, a.h);
-#ifdef PH_HC_RUNTIME
-    g.has_coarse = a.cu != nullptr;
-#else
     g.has_coarse = HC;
-#endif
     g.edge = g.c0 < 0 || g.c0 + PH_PC > a.w;
     const int pair = blockIdx.z;
     const int warp = threadIdx.x >> 5;
@@ -1028,15 +951,10 @@ __global__ void __launch_bounds__(PH_NT, 1) lk_level_phase_kernel(const __grid_c
 #ifndef PH_KNOCK_P3
             phase_vertical<R>(s_prod + voff, tm_mine, v_task);
 #endif
-#ifdef PH_NAMED_BARRIERS
-            asm volatile("bar.arrive 1, %0;" ::"n"(PH_NT) : "memory");
-            asm volatile("bar.sync 2, %0;" ::"n"(V_WARPS * 32) : "memory");   // P3 done in all V warps
-#else
             // "my part of P3 is done": an arrival on a shared-memory barrier, which nobody waits for before P4,
             // so that a V warp goes on to its P1 row at once instead of waiting for the slowest V warp here
             __syncwarp();
             if ((threadIdx.x & 31) == 0) mbar_arrive(s_p3bar);
-#endif
         }
         PH_MARK(2);
         {
@@ -1045,12 +963,8 @@ __global__ void __launch_bounds__(PH_NT, 1) lk_level_phase_kernel(const __grid_c
         }
         PH_MARK(3);
         if (s >= 0) {
-#ifdef PH_NAMED_BARRIERS
-            if (warp >= V_WARPS) asm volatile("bar.sync 1, %0;" ::"n"(PH_NT) : "memory");
-#else
             if (p4_idx >= 0) mbar_wait(s_p3bar, p3_par);     // P3 done in all V warps
             p3_par ^= 1u;
-#endif
             PH_MARK(4);
 #ifndef PH_KNOCK_P4
             if (p4_idx >= 0)
@@ -1101,11 +1015,7 @@ __global__ void __launch_bounds__(PhaseCfg<1>::NT, PhaseCfg<1>::CTAS)
     g.c0 = g.xo0 - 4 * C::HL;
     g.y0 = blockIdx.y * th;
     g.y1 = min(g.y0 + th, a.h);
-#ifdef PH_HC_RUNTIME
-    g.has_coarse = a.cu != nullptr;
-#else
     g.has_coarse = HC;
-#endif
     g.edge = g.c0 < 0 || g.c0 + PH_PC > a.w;
     const int pair = blockIdx.z;
 
