@@ -57,3 +57,32 @@ def test_product_never_imports_oracle():
                 txt = open(os.path.join(dp, f)).read()
                 assert "lk_oracle" not in txt and "c_oracle" not in txt and "live_oracle" not in txt, f
                 assert not re.search(r"^\s*(from|import)\s+oracle\b", txt, re.M), f
+
+
+def test_mgpu_partition_host_function(ofb):
+    """of_mgpu_partition (host arithmetic): contiguous blocks that cover every pair once, sizes within one."""
+    for n in (0, 1, 7, 63, 194):
+        for nd in (1, 2, 3, 4, 8):
+            got, sizes = [], []
+            for i in range(nd):
+                a, b = ofb.MultiGpu.partition(n, nd, i)
+                assert 0 <= a <= b <= n
+                got += list(range(a, b))
+                sizes.append(b - a)
+            assert got == list(range(n)) and max(sizes) - min(sizes) <= 1
+    with pytest.raises(ofb.BadArgError):
+        ofb.MultiGpu.partition(4, 2, 2)
+
+
+def test_live_params_default_are_the_reference_constants(ofb):
+    # ParallelVideoPyr.cpp:728-729 (DIFF_THRESH 10, LEARNING_RATE 0.3), :782 (1080 x 1080), :790 (9, 1.5), :812-813 (2)
+    lp = ofb.OfLiveParams()
+    ofb.lib().of_live_params_default(C.byref(lp))
+    assert (lp.work_width, lp.work_height, lp.blur_ksize, lp.blur_sigma, lp.learning_rate, lp.diff_thresh,
+            lp.morph_iterations, lp.n_levels) == (1080, 1080, 9, 1.5, 0.3, 10, 2, 0)
+    assert lp.coeff_bits == 14                       # OpenCV 2.4's cvtColor table, the reference's library
+
+
+def test_static_scratch_limit_is_declared(ofb):
+    txt = open(os.path.join(ROOT, "include", "of_b200.h")).read()
+    assert re.search(r"#define\s+OF_STATIC_SCRATCH_BYTES\s+\(32u << 20\)", txt)
