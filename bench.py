@@ -504,7 +504,14 @@ def run_ours(args):
             for k in range(n8t):
                 CO.coarse_to_fine(frames_h[k], frames_h[k + 1], LEVELS, radius)
             v8 = n8t / (time.perf_counter() - t0)
+            CO.set_threads(host_threads())
+            n31 = 16 if W * H <= 1920 * 1080 else 4
+            t0 = time.perf_counter()
+            for k in range(n31):
+                CO.coarse_to_fine(frames_h[k % pairs], frames_h[k % pairs + 1], LEVELS, 1)
+            v31 = n31 / (time.perf_counter() - t0)
             cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "value_8_threads": v8,
+                   "value_3x3_window": v31,
                    "sample": "%d pairs (the first %d consecutive pairs of the same synthetic stream, L=%d, r=%d, cycled), "
                              "oracle/lk_oracle.c C+OpenMP port of the reference path, all host threads, %.1f s"
                              % (n_cpu, pairs, LEVELS, radius, secs)}
